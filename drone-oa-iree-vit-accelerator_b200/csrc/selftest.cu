@@ -1,0 +1,307 @@
+// selftest.cu -- GPU self-tests of the tcgen05 building blocks the fused kernel relies on (shared-memory descriptor
+// geometry for K-major and MN-major int8 operands, mixed u8 x s8, TMEM load mapping, 2-D TMA panel loads), and the
+// micro-benchmarks that provide roofline denominators (dense kind::i8 issue rate).
+#include <stdarg.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace ita {
+
+int make_x_tensor_map(CUtensorMap *map, const void *x, long long rows, int row_bytes);   // fused.cu
+
+// D[128,N] (s32) = A[128,K] . B, one CTA.
+//   A: row-major [128,K] (s8 or u8), staged into the K-major panel layout by threads or by 2-D TMA.
+//   B: b_mn == 0: row-major [N,K] ("K-major operand"),  b_mn == 1: row-major [K,N] ("MN-major operand", like V [S,P]).
+__global__ void __launch_bounds__(128) k_umma_test(const __grid_constant__ CUtensorMap amap, const int8_t *A, const int8_t *Bm,
+                                                   int32_t *D, int N, int K, int a_signed, int b_mn, int use_tma, int *abort_flag) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar_mma, bar_tma;
+  __shared__ uint32_t s_tmem;
+  uint8_t *sA = smem;                 // 128*K bytes, panels [K/16][128][16]
+  uint8_t *sB = smem + 128 * K;       // N*K bytes
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    mbar_init(&bar_mma, 1);
+    mbar_init(&bar_tma, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc<256>(&s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  if (use_tma) {
+    if (tid == 0) {
+      mbar_arrive_expect_tx(&bar_tma, 128 * K);
+      for (int c = 0; c < K / 16; ++c) tma_load_2d(sA + c * 128 * 16, &amap, c * 16, 0, &bar_tma);
+    }
+  } else {
+    for (int i = tid; i < 128 * K; i += 128) {
+      int r = i / K, c = i % K;
+      sA[(c / 16) * 128 * 16 + r * 16 + (c % 16)] = (uint8_t)A[i];
+    }
+  }
+  if (!b_mn) {
+    for (int i = tid; i < N * K; i += 128) {
+      int n = i / K, k = i % K;
+      sB[(k / 16) * N * 16 + n * 16 + (k % 16)] = (uint8_t)Bm[i];
+    }
+  } else {
+    for (int i = tid; i < N * K; i += 128) {
+      int k = i / N, n = i % N;
+      sB[(n / 16) * K * 16 + k * 16 + (n % 16)] = (uint8_t)Bm[i];
+    }
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
+  bool ok = true;
+  if (tid == 0) {
+    if (use_tma) ok = mbar_wait(&bar_tma, 0, abort_flag);
+    tc_fence_after();
+    const uint32_t idesc = make_idesc_i8(128, N, a_signed, 1, 0, b_mn);
+    const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+    for (int k = 0; k < K / 32; ++k) {
+      const uint64_t ad = make_smem_desc(a_addr + k * 2 * 128 * 16, 128 * 16, 128);
+      const uint64_t bd = b_mn ? make_smem_desc(b_addr + k * 32 * 16, 128, K * 16) : make_smem_desc(b_addr + k * 2 * N * 16, N * 16, 128);
+      umma_i8(tmem, ad, bd, idesc, k > 0);
+    }
+    umma_commit(&bar_mma);
+  }
+  ok = mbar_wait(&bar_mma, 0, abort_flag) && ok;
+  tc_fence_after();
+  if (ok) {
+    const int row = warp * 32 + lane;
+    for (int c = 0; c < N; c += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + c, v);
+      tmem_ld_wait();
+      for (int j = 0; j < 16; ++j) D[row * N + c + j] = (int32_t)v[j];
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem);
+  }
+}
+
+// Dense kind::i8 issue-rate benchmark: every CTA loops MMAs (M=128, N=256, K=32) over resident shared-memory operands.
+__global__ void __launch_bounds__(128) k_umma_peak(int iters, int *abort_flag) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < (128 + 256) * 128 / 4; i += 128) reinterpret_cast<uint32_t *>(smem)[i] = 0x01010101u * (i & 3);
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc<512>(&s_tmem);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  if (tid == 0) {
+    const uint32_t idesc = make_idesc_i8(128, 256, 1, 1, 0, 0);
+    const uint32_t a_addr = smem_u32(smem), b_addr = a_addr + 128 * 128;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)   // K = 128 per iteration, two accumulator buffers alternate
+        umma_i8(tmem + (it & 1) * 256, make_smem_desc(a_addr + k * 2 * 128 * 16, 128 * 16, 128),
+                make_smem_desc(b_addr + k * 2 * 256 * 16, 256 * 16, 128), idesc, 1);
+    }
+    umma_commit(&bar);
+    mbar_wait(&bar, 0, abort_flag);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem);
+  }
+}
+
+static void appendf(std::string &s, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  s += buf;
+}
+
+int selftest_run(int device, std::string &rep) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    set_error("ita_selftest: no CUDA device");
+    rep = "no CUDA device\n";
+    return ITA_ERR_CUDA;
+  }
+  if (device < 0) device = 0;
+  ITA_CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  ITA_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  appendf(rep, "device %d: %s, sm_%d%d, %d SMs\n", device, prop.name, prop.major, prop.minor, prop.multiProcessorCount);
+  if (prop.major != 10) {
+    appendf(rep, "not an sm_100 device: tcgen05 self-tests skipped\n");
+    set_error("ita_selftest: not an sm_100 device");
+    return ITA_ERR_UNSUPPORTED;
+  }
+  struct Case { int N, K, a_signed, b_mn, use_tma; const char *what; };
+  const Case cases[] = {
+      {192, 64, 1, 0, 0, "projection  X.W^T     s8 x s8, K-major B"},
+      {128, 192, 1, 0, 0, "logits      Q.K^T     s8 x s8, K-major B"},
+      {192, 128, 0, 1, 0, "context     Asm.V     u8 x s8, MN-major B"},
+      {64, 192, 1, 0, 0, "out-proj    O.Wo      s8 x s8, K-major B"},
+      {192, 64, 1, 0, 1, "projection with A through 2-D TMA panel loads"},
+      {64, 128, 0, 1, 0, "context     Asm.V     u8 x s8, MN-major B, N=64"},
+      {256, 32, 1, 0, 0, "N=256 K=32 single MMA"},
+  };
+  int *abort_flag = nullptr;
+  ITA_CUDA_TRY(cudaMalloc(&abort_flag, sizeof(int)));
+  ITA_CUDA_TRY(cudaMemset(abort_flag, 0, sizeof(int)));
+  ITA_CUDA_TRY(cudaFuncSetAttribute((const void *)k_umma_test, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  int failures = 0;
+  unsigned seed = 12345;
+  auto rnd = [&]() { seed = seed * 1664525u + 1013904223u; return (int)((seed >> 16) & 0xFF); };
+  for (const Case &c : cases) {
+    const int N = c.N, K = c.K;
+    std::vector<int8_t> A(128 * K), Bm((size_t)N * K);
+    for (auto &v : A) v = (int8_t)rnd();
+    for (auto &v : Bm) v = (int8_t)rnd();
+    std::vector<int32_t> ref((size_t)128 * N), got((size_t)128 * N);
+    for (int m = 0; m < 128; ++m)
+      for (int n = 0; n < N; ++n) {
+        int acc = 0;
+        for (int k = 0; k < K; ++k) {
+          int a = c.a_signed ? (int)A[m * K + k] : (int)(uint8_t)A[m * K + k];
+          int b = c.b_mn ? (int)Bm[(size_t)k * N + n] : (int)Bm[(size_t)n * K + k];
+          acc += a * b;
+        }
+        ref[(size_t)m * N + n] = acc;
+      }
+    int8_t *dA = nullptr, *dB = nullptr;
+    int32_t *dD = nullptr;
+    ITA_CUDA_TRY(cudaMalloc(&dA, A.size()));
+    ITA_CUDA_TRY(cudaMalloc(&dB, Bm.size()));
+    ITA_CUDA_TRY(cudaMalloc(&dD, got.size() * 4));
+    ITA_CUDA_TRY(cudaMemcpy(dA, A.data(), A.size(), cudaMemcpyHostToDevice));
+    ITA_CUDA_TRY(cudaMemcpy(dB, Bm.data(), Bm.size(), cudaMemcpyHostToDevice));
+    ITA_CUDA_TRY(cudaMemset(dD, 0xCD, got.size() * 4));
+    CUtensorMap map;
+    memset(&map, 0, sizeof(map));
+    int rc = make_x_tensor_map(&map, dA, 128, K);
+    if (rc) return rc;
+    k_umma_test<<<1, 128, 128 * K + N * K, 0>>>(map, dA, dB, dD, N, K, c.a_signed, c.b_mn, c.use_tma, abort_flag);
+    count_launch();
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+      appendf(rep, "FAIL  %-52s CUDA error: %s\n", c.what, cudaGetErrorString(e));
+      set_error("ita_selftest: kernel failed: %s", cudaGetErrorString(e));
+      return ITA_ERR_CUDA;
+    }
+    int flag = 0;
+    ITA_CUDA_TRY(cudaMemcpy(&flag, abort_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    ITA_CUDA_TRY(cudaMemcpy(got.data(), dD, got.size() * 4, cudaMemcpyDeviceToHost));
+    size_t bad = 0, first = (size_t)-1;
+    for (size_t i = 0; i < got.size(); ++i)
+      if (got[i] != ref[i]) {
+        if (first == (size_t)-1) first = i;
+        ++bad;
+      }
+    if (flag || bad) {
+      ++failures;
+      appendf(rep, "FAIL  %-52s N=%d K=%d: %zu/%zu mismatches%s", c.what, N, K, bad, got.size(), flag ? " (wait timed out)" : "");
+      if (bad) appendf(rep, ", first at (m=%zu,n=%zu): got %d want %d", first / N, first % N, got[first], ref[first]);
+      appendf(rep, "\n");
+      ITA_CUDA_TRY(cudaMemset(abort_flag, 0, sizeof(int)));
+    } else {
+      appendf(rep, "ok    %-52s N=%d K=%d\n", c.what, N, K);
+    }
+    cudaFree(dA); cudaFree(dB); cudaFree(dD);
+  }
+  cudaFree(abort_flag);
+  if (failures) {
+    set_error("ita_selftest: %d case(s) failed", failures);
+    return ITA_ERR_CUDA;
+  }
+  return ITA_OK;
+}
+
+int microbench_run(int device, int kind, double *out, int n_out) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    set_error("ita_microbench: no CUDA device");
+    return ITA_ERR_CUDA;
+  }
+  if (device < 0) device = 0;
+  ITA_CUDA_TRY(cudaSetDevice(device));
+  int sms = 0, major = 0;
+  ITA_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  ITA_CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  cudaEvent_t e0, e1;
+  ITA_CUDA_TRY(cudaEventCreate(&e0));
+  ITA_CUDA_TRY(cudaEventCreate(&e1));
+  if (kind == 0) {
+    if (major != 10) {
+      set_error("ita_microbench: kind 0 needs an sm_100 device");
+      return ITA_ERR_UNSUPPORTED;
+    }
+    int *abort_flag = nullptr;
+    ITA_CUDA_TRY(cudaMalloc(&abort_flag, sizeof(int)));
+    ITA_CUDA_TRY(cudaMemset(abort_flag, 0, sizeof(int)));
+    const int smem = (128 + 256) * 128;
+    ITA_CUDA_TRY(cudaFuncSetAttribute((const void *)k_umma_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int iters = 20000;
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+      ITA_CUDA_TRY(cudaEventRecord(e0));
+      k_umma_peak<<<sms, 128, smem>>>(iters, abort_flag);
+      count_launch();
+      ITA_CUDA_TRY(cudaEventRecord(e1));
+      ITA_CUDA_TRY(cudaEventSynchronize(e1));
+      float ms = 0;
+      ITA_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+      double ops = 2.0 * 128 * 256 * 128 * (double)iters * sms;
+      double tops = ops / (ms * 1e-3) / 1e12;
+      if (rep > 0 && tops > best) best = tops;
+    }
+    out[0] = best;
+    if (n_out > 1) out[1] = sms;
+    cudaFree(abort_flag);
+  } else if (kind == 1) {
+    const size_t bytes = size_t(1) << 30;
+    void *a = nullptr, *b = nullptr;
+    ITA_CUDA_TRY(cudaMalloc(&a, bytes));
+    ITA_CUDA_TRY(cudaMalloc(&b, bytes));
+    ITA_CUDA_TRY(cudaMemset(a, 1, bytes));
+    double best = 0;
+    for (int rep = 0; rep < 5; ++rep) {
+      ITA_CUDA_TRY(cudaEventRecord(e0));
+      ITA_CUDA_TRY(cudaMemcpyAsync(b, a, bytes, cudaMemcpyDeviceToDevice, 0));
+      ITA_CUDA_TRY(cudaEventRecord(e1));
+      ITA_CUDA_TRY(cudaEventSynchronize(e1));
+      float ms = 0;
+      ITA_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+      double gbs = 2.0 * bytes / (ms * 1e-3) / 1e9;
+      if (rep > 0 && gbs > best) best = gbs;
+    }
+    out[0] = best;
+    cudaFree(a); cudaFree(b);
+  } else {
+    set_error("ita_microbench: unknown kind %d", kind);
+    return ITA_ERR_INVALID;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return ITA_OK;
+}
+
+}  // namespace ita

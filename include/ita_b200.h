@@ -1,0 +1,158 @@
+/* ita_b200.h -- C-ABI of libita_b200.so: the B200 (sm_100a) implementation of the ITA int8 multi-head attention.
+ *
+ * This is the drop-in boundary for ONE hot path of OpenHardware-Initiative/Drone-OA-IREE-ViT-Accelerator: the ITA
+ * attention block that ITAViTLSTM offloads.  Plain C types only (no torch / CUDA types in any signature); every
+ * function returns 0 on success and non-zero on error (the IREE dispatch convention: a non-zero return from the
+ * enclosing dispatch function means failure, third_party/iree/runtime/src/iree/hal/local/executable_library.h:362-371).
+ * ita_last_error() returns a thread-local message for the last failing call.
+ *
+ * Which reference interface each entry point replaces (paths relative to the reference repo):
+ *
+ *   ita_mha_create / ita_mha_destroy
+ *       the golden-model constructor  Transformer(ITA_N, path, activation, S,P,E,F,H, Q,K,V, Wq,Wk,Wv,Wo, Bq,Bk,Bv,Bo,
+ *       FF_in,Wff,Wff2,Bff,Bff2, quant_params=...)      tests/export_and_validation_W_B.py:518 (tensor layouts :479-491,
+ *       quant_params dict :247-305) and the parameter-carrying half of ITASelfAttention_QAT.__init__
+ *       models/ITA/QAT/layers.py:79-99.
+ *   ita_mha_forward
+ *       ITASelfAttention_QAT.forward between the quant stub and the dequant stub   models/ITA/QAT/layers.py:103-126,
+ *       == step1_Qp..step6_O(/step7_Osum) of the golden model  tests/export_and_validation_W_B.py:520-542,
+ *       == what the IREE custom dispatch  void ITASelfAttention_workgroup(const T* input, T* output)  is meant to
+ *       compute   samples/inference_udp_FPGA_custom_dispatch/plugin/ITA_dispatch.c:17-27 (decl ITA_spec.mlir:30-33):
+ *       caller-owned in/out buffers of shape [B,S,E], no aliasing.
+ *   ita_mha_forward_host
+ *       the same call for a caller that owns HOST buffers (what main.cpp hands to iree_runtime_call_invoke,
+ *       samples/inference_udp_FPGA_custom_dispatch/main.cpp:168-195): H2D copy, kernels, D2H copy, synchronous.
+ *   ita_mha_forward_stages
+ *       the per-stage attributes the reference harness reads from the golden model: Qp_requant, Kp_requant, Vp_requant,
+ *       A_requant, A_partial_softmax, O_soft_requant, Out_soft_requant   tests/export_and_validation_W_B.py:520-542.
+ *   ita_mha_step
+ *       one golden-model step (step1_Qp ... step6_O) on caller-provided stage inputs, so that the harness' pattern
+ *       "overwrite A_partial_softmax, then call step5_AV" (tests/export_and_validation_W_B.py:531-540) keeps working.
+ *   ita_ffn_forward
+ *       ITAFeedForward_QAT.forward  models/ITA/QAT/layers.py:61-75 == golden feedforward_layer
+ *       tests/export_and_validation_W_B.py:544-553.
+ *   ita_quantize_f32 / ita_dequantize_s8
+ *       the QuantStub / DeQuantStub at the float boundary of the operator   models/ITA/QAT/layers.py:103,126.
+ *
+ * Threading: a handle may be used from one host thread at a time; distinct handles are independent.  All device work
+ * of a call is enqueued on the CUDA stream passed in (a cudaStream_t cast to void*; NULL = the legacy default stream)
+ * and, except for the *_host entry points, the call returns without synchronising.
+ */
+#ifndef ITA_B200_H_
+#define ITA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ITA_B200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define ITA_API __attribute__((visibility("default")))
+#else
+#define ITA_API
+#endif
+
+/* requant rounding */
+enum { ITA_ROUND_HALF_UP = 0, ITA_ROUND_FLOOR = 1, ITA_ROUND_TORCH_RNE_F32 = 2 };
+/* ITAmax variant */
+enum { ITA_SOFTMAX_REPO_GLOBAL = 0, ITA_SOFTMAX_STREAM16 = 1 };
+/* multi-head convention */
+enum { ITA_HEADS_PYITA = 0, ITA_HEADS_TORCH = 1 };
+/* requant stages: index into mult/shift/add/eff[stage*H + head]; 0..6 is the golden model's order */
+enum { ITA_ST_Q = 0, ITA_ST_K, ITA_ST_V, ITA_ST_QK, ITA_ST_AV, ITA_ST_O, ITA_ST_SUM, ITA_ST_FC1, ITA_ST_RELU, ITA_ST_FC2,
+       ITA_NUM_STAGES };
+/* golden-model steps for ita_mha_step */
+enum { ITA_STEP1_QP = 1, ITA_STEP2_KP = 2, ITA_STEP3_VP = 3, ITA_STEP4_QK = 4, ITA_STEP4_SOFTMAX = 40, ITA_STEP5_AV = 5,
+       ITA_STEP6_O = 6, ITA_STEP7_OSUM = 7 };
+/* which kernels a forward call uses */
+enum { ITA_PATH_AUTO = 0,     /* fused tcgen05 kernel when the shape/params are supported, else the staged kernels */
+       ITA_PATH_FUSED = 1,    /* fused tcgen05 kernel; error if unsupported                                        */
+       ITA_PATH_STAGED = 2 }; /* one kernel per stage, every intermediate written to HBM scratch                    */
+
+/* error codes */
+enum { ITA_OK = 0, ITA_ERR_INVALID = 1, ITA_ERR_UNSUPPORTED = 2, ITA_ERR_CUDA = 3, ITA_ERR_NOMEM = 4 };
+
+/* All pointers in the descriptor are HOST pointers; the handle keeps device copies.  Layouts are the golden model's
+ * (tests/export_and_validation_W_B.py:479-491): Wq/Wk/Wv [H,E,P] s8, Wo [H,P,E] s8, Bq/Bk/Bv [H,P] s32, Bo [H,E] s32,
+ * Wff [1,E,F], Wff2 [1,F,E], Bff [1,F], Bff2 [1,E].  P is the per-head projection width. */
+typedef struct ita_mha_desc {
+  int32_t abi_version;          /* ITA_B200_ABI_VERSION */
+  int32_t S, E, P, H, F;        /* F == 0: no FFN parameters */
+  int32_t round_mode, softmax_mode, head_mode;
+  int32_t device;               /* CUDA device ordinal, -1 = current device */
+  const int8_t *Wq, *Wk, *Wv, *Wo;
+  const int32_t *Bq, *Bk, *Bv, *Bo;
+  const int8_t *Wff, *Wff2;     /* may be NULL when F == 0 */
+  const int32_t *Bff, *Bff2;
+  const int32_t *mult, *shift, *add;  /* [ITA_NUM_STAGES, H] */
+  const float *eff;                   /* [ITA_NUM_STAGES, H]; required for ITA_ROUND_TORCH_RNE_F32, else may be NULL */
+} ita_mha_desc;
+
+typedef struct ita_mha_handle ita_mha_handle;
+
+/* Device pointers to per-stage results (any may be NULL = not wanted).  Shapes: Qp/Kp/Vp/O [B,H,S,P] s8,
+ * A [B,H,S,S] s8, Asm [B,H,S,S] u8, Out [B,H,S,E] s8 (ITA_HEADS_TORCH: [B,1,S,E]). */
+typedef struct ita_mha_stages {
+  int8_t *Qp, *Kp, *Vp, *A;
+  uint8_t *Asm;
+  int8_t *O, *Out;
+} ita_mha_stages;
+
+ITA_API int ita_b200_abi_version(void);
+ITA_API const char *ita_last_error(void);
+/* number of CUDA kernels this library has launched in the calling process since load (for bench.py's gpu_launches) */
+ITA_API int64_t ita_kernel_launch_count(void);
+
+ITA_API int ita_mha_create(const ita_mha_desc *desc, ita_mha_handle **out);
+ITA_API void ita_mha_destroy(ita_mha_handle *h);
+/* 1 if the fused tcgen05 kernel can run this handle's shape and parameters, else 0 (reason in ita_last_error()) */
+ITA_API int ita_mha_fused_supported(const ita_mha_handle *h);
+
+/* x_dev [batch,S,E] s8 -> y_dev [batch,S,E] s8, both DEVICE pointers; asynchronous on `cuda_stream`. */
+ITA_API int ita_mha_forward(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64_t batch, int32_t path, void *cuda_stream);
+/* same with HOST pointers (pinned or pageable): H2D, kernels, D2H, then synchronises the stream. */
+ITA_API int ita_mha_forward_host(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host, int64_t batch, int32_t path,
+                         void *cuda_stream);
+/* staged kernels; writes every requested intermediate (DEVICE pointers) and y_dev (may be NULL). */
+ITA_API int ita_mha_forward_stages(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64_t batch,
+                           const ita_mha_stages *stages, void *cuda_stream);
+/* Diagnostic twin of ita_mha_forward_stages: runs the FUSED kernel and additionally dumps its on-chip intermediates
+ * (Qp, Kp, Vp, A, Asm, O; `Out` is ignored) in the natural layouts.  Synchronises the stream. */
+ITA_API int ita_mha_forward_fused_debug(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64_t batch,
+                                const ita_mha_stages *stages, void *cuda_stream);
+/* Synchronise `cuda_stream` and report (and clear) a device-side pipeline time-out raised by earlier asynchronous
+ * forward calls on this handle (every in-kernel wait is bounded; a protocol error surfaces here, not as a hang). */
+ITA_API int ita_mha_sync_check(ita_mha_handle *h, void *cuda_stream);
+/* One golden-model step on DEVICE buffers laid out as in ita_mha_stages; `in0`/`in1` are the step's inputs:
+ *   STEP1/2/3: in0 = X [B,S,E]                       -> out [B,H,S,P]
+ *   STEP4_QK : in0 = Qp, in1 = Kp                    -> out = A [B,H,S,S] s8
+ *   STEP4_SOFTMAX: in0 = A                           -> out = Asm (u8)
+ *   STEP5_AV : in0 = Asm (u8), in1 = Vp              -> out = O
+ *   STEP6_O  : in0 = O                               -> out = Out [B,H,S,E] (HEADS_TORCH: Y [B,S,E])
+ *   STEP7_OSUM: in0 = Out                            -> out = Y [B,S,E]                                              */
+ITA_API int ita_mha_step(ita_mha_handle *h, int32_t step, const void *in0, const void *in1, void *out, int64_t batch,
+                 void *cuda_stream);
+
+/* FFN block: x_dev [batch,S,E] s8 -> f2_dev [batch,S,E] s8; f1_dev ([batch,S,F] s8, post-ReLU) may be NULL. */
+ITA_API int ita_ffn_forward(ita_mha_handle *h, const int8_t *x_dev, int8_t *f1_dev, int8_t *f2_dev, int64_t batch, void *cuda_stream);
+
+/* float boundary: q = sat8(rne(x / scale)),  y = scale * q   (n elements, DEVICE pointers) */
+ITA_API int ita_quantize_f32(const float *x_dev, int8_t *q_dev, int64_t n, float scale, void *cuda_stream);
+ITA_API int ita_dequantize_s8(const int8_t *q_dev, float *y_dev, int64_t n, float scale, void *cuda_stream);
+
+/* GPU self-tests of the tcgen05 building blocks (descriptor layouts, TMEM load, TMA).  Returns 0 when every check
+ * passes; a human-readable report is written into `report` (NUL-terminated, at most report_len bytes). */
+ITA_API int ita_selftest(int32_t device, char *report, int64_t report_len);
+
+/* Micro-benchmarks used by bench.py for the roofline denominators (results in `out`):
+ *   kind 0: dense tcgen05 kind::i8 MMA issue rate -> out[0] = int8 TOP/s over the whole GPU
+ *   kind 1: device-to-device copy                 -> out[0] = GB/s (read+write)                                     */
+ITA_API int ita_microbench(int32_t device, int32_t kind, double *out, int32_t n_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ITA_B200_H_ */
