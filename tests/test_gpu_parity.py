@@ -1,0 +1,328 @@
+"""GPU parity tests (run on the B200 box with ``-m gpu``): every CUDA path of libita_b200.so, called through the C-ABI
+(ctypes -> ``ITAEngine``), against the CPU oracle on identical seeded inputs, against the committed golden fixtures that
+were generated from the importable reference, and -- at BASELINE.json's full sizes -- through size-independent
+properties (fused == staged, batch-permutation equivariance, duplicate frames).
+
+Bar: bit-exact (integer path).  Nothing here reads /root/reference.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, to_engine_params
+
+torch = pytest.importorskip("torch")
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not torch.cuda.is_available(), reason="needs a CUDA device")]
+
+STAGES = ("Qp", "Kp", "Vp", "A", "Asm", "O", "Y")
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _engine(ita, p):
+    return ita.ITAEngine(to_engine_params(ita, p), _dev())
+
+
+def _cmp(got, want, what):
+    got = got.cpu().numpy() if hasattr(got, "cpu") else got
+    want = want.reshape(got.shape)
+    bad = int((got != want).sum())
+    assert bad == 0, f"{what}: {bad}/{got.size} mismatches, first at {np.argwhere(got != want)[:3].tolist()}"
+
+
+# ----------------------------------------------------------------------------------------------------- building blocks
+def test_tcgen05_selftest(ita):
+    """Descriptor geometry (K-major / MN-major int8 operands, u8 x s8), TMEM load mapping and 2-D TMA panel loads."""
+    rep = ita.selftest(0)
+    assert "FAIL" not in rep, rep
+
+
+# ----------------------------------------------------------------------------------------------------- staged kernels
+@pytest.mark.parametrize("dims", [(64, 64, 64, 1), (128, 64, 192, 1), (128, 128, 192, 1), (256, 128, 64, 4), (32, 32, 32, 2),
+                                  (48, 40, 24, 3)])
+@pytest.mark.parametrize("round_mode", [0, 1, 2])
+@pytest.mark.parametrize("softmax_mode", [0, 1])
+def test_staged_all_stages_vs_oracle(ita, R, dims, round_mode, softmax_mode):
+    S, E, P, H = dims
+    for head_mode in ((0, 1) if H > 1 else (0,)):
+        p = R.make_synthetic(S, E, P, H, seed=11, rand_add=True, round_mode=round_mode, softmax_mode=softmax_mode,
+                             head_mode=head_mode)
+        X = R.make_input(3, S, E, seed=21)
+        ref = R.mha_forward(p, X)
+        eng = _engine(ita, p)
+        st = eng.forward_stages(torch.from_numpy(X).to(_dev()))
+        for k in STAGES + ("Out",):
+            _cmp(st[k], ref[k], f"staged {k} dims={dims} round={round_mode} softmax={softmax_mode} heads={head_mode}")
+        y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_STAGED)
+        _cmp(y, ref["Y"], "staged forward Y")
+        eng.close()
+
+
+# ----------------------------------------------------------------------------------------------------- fused kernel
+FUSED_SHAPES = [(64, 192), (64, 64), (64, 128), (128, 64), (128, 192), (128, 128)]
+
+
+@pytest.mark.parametrize("EP", FUSED_SHAPES)
+@pytest.mark.parametrize("round_mode", [0, 1, 2])
+@pytest.mark.parametrize("softmax_mode", [0, 1])
+def test_fused_every_intermediate_vs_oracle(ita, R, EP, round_mode, softmax_mode):
+    """The fused tcgen05 kernel with its on-chip intermediates dumped: every stage bit-exact, ragged batch (7 frames)."""
+    E, P = EP
+    p = R.make_synthetic(128, E, P, 1, seed=5, rand_add=True, round_mode=round_mode, softmax_mode=softmax_mode)
+    eng = _engine(ita, p)
+    if not eng.fused_supported:
+        pytest.skip("fused kernel not instantiated for this shape: " + eng.fused_unsupported_reason())
+    X = R.make_input(7, 128, E, seed=31)
+    ref = R.mha_forward(p, X)
+    st = eng.forward_stages(torch.from_numpy(X).to(_dev()), fused_debug=True)
+    for k in STAGES:
+        _cmp(st[k], ref[k], f"fused {k} E={E} P={P} round={round_mode} softmax={softmax_mode}")
+    y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
+    eng.sync_check()
+    _cmp(y, ref["Y"], "fused forward Y")
+    eng.close()
+
+
+@pytest.mark.parametrize("batch", [0, 1, 2, 3, 295, 296, 297, 1000])
+def test_fused_batch_sizes(ita, R, RC, batch):
+    """Empty, single, odd, exactly one wave (2 x 148), one more, and multi-wave batches."""
+    p = R.make_synthetic(128, 64, 192, 1, seed=0)
+    eng = _engine(ita, p)
+    assert eng.fused_supported, eng.fused_unsupported_reason()
+    X = R.make_input(batch, 128, 64, seed=batch)
+    y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
+    eng.sync_check()
+    assert tuple(y.shape) == (batch, 128, 64)
+    if batch:
+        _cmp(y, RC.mha(p, X, intermediates=False)["Y"], f"fused batch={batch}")
+    eng.close()
+
+
+def test_fused_general_requant_ranges(ita, R, RC):
+    """Parameter sets outside the fast `hi32` requant form (small shifts, large multipliers) take the general form."""
+    p = R.make_synthetic(128, 64, 192, 1, seed=9)
+    p.mult = p.mult * 2
+    p.shift = p.shift + 1          # same rational, mult > 255 => general path
+    p.mult[R.ST_QK] = 3
+    p.shift[R.ST_QK] = 5
+    eng = _engine(ita, p)
+    X = R.make_input(5, 128, 64, seed=2)
+    ref = RC.mha(p, X)
+    if eng.fused_supported:
+        st = eng.forward_stages(torch.from_numpy(X).to(_dev()), fused_debug=True)
+        for k in STAGES:
+            _cmp(st[k], ref[k], f"fused(general requant) {k}")
+    st = eng.forward_stages(torch.from_numpy(X).to(_dev()))
+    for k in STAGES:
+        _cmp(st[k], ref[k], f"staged(general requant) {k}")
+    eng.close()
+
+
+def test_edge_inputs(ita, R, RC):
+    """Saturating inputs, all-equal logit rows, one-hot rows: all-zero / all-extreme frames and weights."""
+    p = R.make_synthetic(128, 64, 192, 1, seed=4)
+    X = np.zeros((6, 128, 64), np.int8)
+    X[1] = 127
+    X[2] = -128
+    X[3, ::2] = 127
+    X[3, 1::2] = -128
+    X[4, 0] = 127                      # one token dominates
+    X[5] = R.make_input(1, 128, 64, seed=8)[0]
+    eng = _engine(ita, p)
+    ref = RC.mha(p, X)
+    for fused in ((True, False) if eng.fused_supported else (False,)):
+        st = eng.forward_stages(torch.from_numpy(X).to(_dev()), fused_debug=fused)
+        for k in STAGES:
+            _cmp(st[k], ref[k], f"edge inputs {'fused' if fused else 'staged'} {k}")
+    eng.close()
+    # extreme weights: every accumulator at its bound, requant saturates both ways
+    p2 = R.make_synthetic(128, 64, 192, 1, seed=4)
+    p2.Wq[:] = 127
+    p2.Wk[:] = -128
+    p2.Wv[:, ::2] = 127
+    eng = _engine(ita, p2)
+    ref = RC.mha(p2, X)
+    for fused in ((True, False) if eng.fused_supported else (False,)):
+        st = eng.forward_stages(torch.from_numpy(X).to(_dev()), fused_debug=fused)
+        for k in STAGES:
+            _cmp(st[k], ref[k], f"extreme weights {'fused' if fused else 'staged'} {k}")
+    eng.close()
+
+
+# ----------------------------------------------------------------------------------------------------- golden fixtures
+def _fixture_params(R, q, pre, round_mode):
+    from test_oracle import _block_params
+    return _block_params(R, q, pre, round_mode)
+
+
+@pytest.mark.parametrize("variant,blocks", [("E64", 1), ("E128", 2)])
+def test_reference_fixture_bit_exact_on_gpu(ita, R, variant, blocks):
+    """The converted reference block captured in tests/golden/qat_block_*.npz (generated by importing the reference,
+    tests/golden/make_golden.py): in torch-rounding mode the CUDA paths reproduce EVERY stage bit-exactly."""
+    from test_oracle import STAGE_FIX
+    q = np.load(os.path.join(GOLDEN, f"qat_block_{variant}.npz"))
+    for bi in range(blocks):
+        pre = f"b{bi}_"
+        p = _fixture_params(R, q, pre, R.ROUND_TORCH_RNE_F32)
+        eng = _engine(ita, p)
+        x = torch.from_numpy(q[pre + "x"]).to(_dev())
+        for fused in ((True, False) if eng.fused_supported else (False,)):
+            st = eng.forward_stages(x, fused_debug=fused)
+            for k, fk in STAGE_FIX.items():
+                _cmp(st[k], q[pre + fk], f"fixture {variant} block {bi} {'fused' if fused else 'staged'} {k}")
+        eng.close()
+
+
+def test_itamax_fixture_on_gpu(ita, R):
+    """Reference IntegerApproximatedSoftmaxFn vectors through the CUDA ITAmax step (ita_mha_step STEP4_SOFTMAX)."""
+    g = np.load(os.path.join(GOLDEN, "itamax_repo.npz"))
+    for k in g.files:
+        if not k.startswith("x"):
+            continue
+        x = g[k]
+        rows, S = x.shape
+        p = R.make_synthetic(S, 32, 32, 1, seed=0)
+        eng = _engine(ita, p)
+        # rows are independent: present them as `rows` frames' first logit row, padded to [rows,1,S,S]
+        a = np.zeros((rows, 1, S, S), np.int8)
+        a[:, 0, 0, :] = x
+        out = torch.empty((rows, 1, S, S), dtype=torch.uint8, device=_dev())
+        eng.step(ita._lib.STEP4_SOFTMAX, torch.from_numpy(a).to(_dev()), None, out, rows)
+        _cmp(out[:, 0, 0, :], g["y" + k[1:]], f"itamax fixture {k}")
+        eng.close()
+
+
+def test_ffn_fixture_on_gpu(ita, R, RC):
+    q = np.load(os.path.join(GOLDEN, "qat_block_E64.npz"))
+    p = R.make_synthetic(128, 64, 192, 1, seed=1, F=256, rand_add=True)
+    for rm in (0, 1, 2):
+        p.round_mode = rm
+        X = R.make_input(4, 128, 64, seed=3)
+        eng = _engine(ita, p)
+        f1, f2 = eng.ffn(torch.from_numpy(X).to(_dev()), want_f1=True)
+        ref = RC.ffn(p, X)
+        _cmp(f1, ref["FF1"], f"ffn FF1 round={rm}")
+        _cmp(f2, ref["FF2"], f"ffn FF2 round={rm}")
+        eng.close()
+    assert "b0_fc1_w" in q.files
+
+
+# ----------------------------------------------------------------------------------------------------- host surfaces
+def test_forward_host_and_chunked_pipeline(ita, R, RC):
+    p = R.make_synthetic(128, 64, 192, 1, seed=6)
+    eng = _engine(ita, p)
+    for B in (3, 1500):                      # 1500 >= 1024 takes the 4-chunk copy/compute pipeline
+        X = R.make_input(B, 128, 64, seed=B)
+        want = RC.mha(p, X, intermediates=False)["Y"]
+        y = eng.forward_host(X)
+        _cmp(y, want, f"forward_host pageable B={B}")
+        xp = torch.from_numpy(X).pin_memory()
+        yp = torch.empty_like(xp).pin_memory()
+        eng.forward_host(xp, out=yp)
+        _cmp(yp.numpy(), want, f"forward_host pinned B={B}")
+    eng.close()
+
+
+def test_golden_facade_steps(ita, R):
+    """`Transformer` facade driven exactly like the reference harness (W_B.py:518-542), incl. overwriting
+    A_partial_softmax before step5_AV (:531-540)."""
+    for (S, E, P, H, F) in [(64, 64, 64, 1, 64), (128, 64, 192, 1, 256), (64, 64, 32, 2, 0)]:
+        p = R.make_synthetic(S, E, P, H, seed=13, F=F)
+        X = R.make_input(1, S, E, seed=14)[0]
+        names = ["q_proj", "k_proj", "v_proj", "qk_matmul", "av_matmul", "out_proj", "head_sum", "fc1", "relu", "fc2"]
+        qp = {n: {"mult": p.mult[i].tolist(), "shift": p.shift[i].tolist(), "add": p.add[i].tolist()} for i, n in enumerate(names)}
+        t = ita.Transformer(ITA_N=16, path=None, activation="relu", S=S, P=P, E=E, F=F, H=H, Q=X, K=X, V=X, Wq=p.Wq, Wk=p.Wk,
+                            Wv=p.Wv, Wo=p.Wo, Bq=p.Bq, Bk=p.Bk, Bv=p.Bv, Bo=p.Bo, FF_in=X, Wff=p.Wff, Wff2=p.Wff2, Bff=p.Bff,
+                            Bff2=p.Bff2, quant_params=qp)
+        ref = R.mha_forward(p, X)
+        t.step1_Qp(); t.step2_Kp(); t.step3_Vp(); t.step4_QK(no_partial_softmax=False)
+        _cmp(t.Qp_requant, ref["Qp"], "facade Qp"); _cmp(t.Kp_requant, ref["Kp"], "facade Kp")
+        _cmp(t.Vp_requant, ref["Vp"], "facade Vp"); _cmp(t.A_requant, ref["A"], "facade A")
+        _cmp(t.A_partial_softmax, ref["Asm"], "facade Asm")
+        t.step5_AV(); t.step6_O(); t.step7_Osum()
+        _cmp(t.O_soft_requant, ref["O"], "facade O"); _cmp(t.Out_soft_requant, ref["Out"], "facade Out")
+        _cmp(t.Out_sum_requant, ref["Y"], "facade Y")
+        # inject a different softmax (the harness' --isolate_softmax pattern) and re-run step 5
+        inj = np.roll(ref["Asm"][0], 1, axis=-1)
+        t.A_partial_softmax = inj
+        t.step5_AV()
+        want = np.stack([p.rq(R._mm(inj[h], ref["Vp"][0, h]), R.ST_AV, h) for h in range(H)])
+        _cmp(t.O_soft_requant, want, "facade injected softmax -> O")
+        if F:
+            t.feedforward_layer()
+            rf = R.ffn_forward(p, X)
+            _cmp(t.FFp_requant, rf["FF1"], "facade FF1"); _cmp(t.FF2p_requant, rf["FF2"], "facade FF2")
+
+
+def test_module_surface(ita, R):
+    """ITASelfAttention: same ctor / forward(f32[B,N,E]) -> f32[B,N,E] as ITASelfAttention_QAT (layers.py:79,101-127);
+    quant / dequant stubs bit-exact vs their definition."""
+    q = np.load(os.path.join(GOLDEN, "qat_block_E64.npz"))
+    pre = "b0_"
+    m = ita.ITASelfAttention(64, 192, 1)
+    for name in ("q_proj", "k_proj", "v_proj", "out_proj"):
+        lin = getattr(m, name)
+        lin.weight_int8.copy_(torch.from_numpy(q[pre + name + "_w"]))
+        lin.weight_scale = float(q[pre + name + "_sw"])
+        lin.scale = float(q[pre + name + "_sout"])
+        s_in = float(q[pre + name + "_sin"])
+        lin.bias.copy_(torch.from_numpy(q[pre + name + "_bias_i32"].astype(np.float64) * s_in * lin.weight_scale).float())
+    m.quant.scale = float(q[pre + "q_proj_sin"])
+    m.matmul1.scale = float(q[pre + "qk_sout"])
+    m.matmul2.scale = float(q[pre + "av_sout"])
+    xq = q[pre + "x"]
+    x = torch.from_numpy(xq.astype(np.float32) * np.float32(m.quant.scale)).to(_dev())
+    y = m(x)
+    assert y.dtype == torch.float32 and tuple(y.shape) == tuple(x.shape)
+    want = q[pre + "out_proj_out"].reshape(xq.shape).astype(np.float32) * np.float32(m.out_proj.scale)
+    assert np.array_equal(y.cpu().numpy(), want)
+    yq = m.forward_int8(torch.from_numpy(xq).to(_dev()))
+    _cmp(yq, q[pre + "out_proj_out"], "module forward_int8 vs fixture")
+    with pytest.raises(ValueError):
+        m(torch.zeros(1, 128, 32, device=_dev()))
+    with pytest.raises(ValueError):
+        m(torch.zeros(1, 128, 64))            # CPU tensor: no CPU fallback
+    # quantize: clamp(rne(x/s)); ties to even
+    s = 0.5
+    v = torch.tensor([0.25, 0.75, -0.25, -0.75, 1.25, 1000.0, -1000.0, 0.0], device=_dev())
+    assert ita.quantize(v, s).cpu().tolist() == [0, 2, 0, -2, 2, 127, -128, 0]
+
+
+# ----------------------------------------------------------------------------------------------------- full-size properties
+def test_full_size_properties(ita, R, RC):
+    """BASELINE configs[1] size (4096 frames): fused == staged on every frame, permutation equivariance, duplicate
+    frames give duplicate results, and a 256-frame sample equals the oracle."""
+    p = R.make_synthetic(128, 64, 192, 1, seed=0)
+    eng = _engine(ita, p)
+    assert eng.fused_supported, eng.fused_unsupported_reason()
+    B = 4096
+    X = R.make_input(B, 128, 64, seed=77)
+    X[17] = X[4000]
+    x = torch.from_numpy(X).to(_dev())
+    y = eng.forward(x, path=ita.PATH_FUSED)
+    eng.sync_check()
+    ys = eng.forward(x, path=ita.PATH_STAGED)
+    assert torch.equal(y, ys)
+    assert torch.equal(y[17], y[4000])
+    perm = torch.randperm(B, generator=torch.Generator().manual_seed(1)).to(_dev())
+    yp = eng.forward(x[perm].contiguous(), path=ita.PATH_FUSED)
+    eng.sync_check()
+    assert torch.equal(yp, y[perm])
+    idx = np.arange(0, B, 16)
+    _cmp(y[torch.from_numpy(idx).to(_dev())], RC.mha(p, X[idx], intermediates=False)["Y"], "full-size sample vs oracle")
+    eng.close()
+
+
+def test_multi_head_full_config3_sample(ita, R, RC):
+    """BASELINE configs[2] dims (H=4, S=256, E=128, P=64) on a 64-frame sample, both ITAmax variants."""
+    for sm in (0, 1):
+        p = R.make_synthetic(256, 128, 64, 4, seed=2, softmax_mode=sm)
+        X = R.make_input(64, 256, 128, seed=5)
+        eng = _engine(ita, p)
+        y = eng.forward(torch.from_numpy(X).to(_dev()))
+        eng.sync_check()
+        _cmp(y, RC.mha(p, X, intermediates=False)["Y"], f"config 3 sample softmax={sm}")
+        eng.close()
