@@ -1,0 +1,786 @@
+// fused_kernel.cuh -- the hot path (device code; instantiated per shape by fused_inst_*.cu, host side in fused.cu): one persistent sm_100a kernel that runs a whole ITA attention layer per depth frame
+// (Q/K/V projections, Q.K^T, ITAmax, A.V, output projection, all requantisations) without any intermediate leaving
+// the SM: int8 operands in shared memory, s32 accumulators in tensor memory, tcgen05.mma kind::i8.
+//
+// Data layout in shared memory ("panel" layout, the UMMA no-swizzle canonical layout):
+//   a [R x C] int8 matrix is stored as C/16 panels; panel c holds the 16-byte column chunk c of every row, rows
+//   consecutive:   addr(r, col) = (col/16) * R*16 + r*16 + col%16.
+//   * read as a K-major operand (rows = M or N index, columns = K):  SBO = 128 B (next 8 rows), LBO = R*16 (next 16 k)
+//   * read as an MN-major operand (rows = K index, columns = N):     SBO = R*16 (next 16 n),  LBO = 128 B (next 8 k)
+//   An epilogue thread owns one row (= one TMEM lane) and writes 16 B per 16 columns; a warp's 32 rows are 512
+//   contiguous bytes, so the writes are bank-conflict free, and the same buffer serves as the next MMA's operand:
+//     Q [S,P] -> A operand of Q.K^T (K-major)        K [S,P] -> B operand of Q.K^T (K-major, N = S)
+//     V [S,P] -> B operand of A.V (MN-major: rows are K) Asm [S,S] u8 -> A operand of A.V     O [S,P] -> A operand of O.Wo
+//   Weights are pre-arranged on the host into the same panel layout (W^T as [N rows, K cols]) and bulk-copied once per CTA.
+//
+// Biases ride on the tensor pipe: every weight matrix carries 32 extra K columns holding the int32 bias of its output
+// column as signed base-127 digits (b = g0 + 127 * (g1 + ... + g31)), and the matching A operand of that extra K step
+// is a constant tile whose rows are [1, 127, ..., 127].  The accumulator that reaches the epilogue already contains
+// the bias, so requantisation needs only per-stage *uniform* constants (no per-column loads).
+//
+// Pipeline.  A frame is cut into NCH = 4*P/64 + 4 "chunks", each one accumulator tile of <= 64 columns, in the order
+//     Q[0..NQ) V[0..NQ) K[0..NQ)  S0 S1  AV[0..NQ)  O0 O1            (NQ = P/64; S chunks are 64 key columns, O chunks E/2)
+//   Two frames ("slots") are in flight per SM.  Per slot, TMEM holds a ring of 4 regions x 64 columns; chunk c uses
+//   region c%4.  Each slot has two epilogue warpgroups (4 warps = the 4 TMEM lane quadrants): warpgroup A owns the
+//   logits (both S chunks: a thread holds a whole 128-column row, so ITAmax needs no cross-thread exchange) plus a
+//   share of the other chunks, warpgroup B the rest (Cfg::wg_of).  One MMA-issuing thread per slot walks the chunks in
+//   order, waiting only for (a) the region to be drained and (b) the operand buffers of the chunk to be written
+//   (mbarriers armed by the producing epilogues); a loader thread prefetches the next frame's X tile by TMA.  tcgen05
+//   MMAs of one thread complete in issue order, which is what makes the reuse of the operand buffers (Asm over K, O
+//   over Q, the next X tile in the unused tail of the K buffer) safe.
+//
+// Thread roles (608 threads): warps 0-7 = epilogue of slot 0 (warp w: TMEM lanes 32*(w%4).., warpgroup (w/4)%2),
+// warps 8-15 = slot 1, warps 16/17 = MMA issue for slot 0/1 (one elected thread), warp 18 = TMA loader + TMEM allocator.
+//
+// Reference semantics: models/ITA/QAT/layers.py:103-126 and tests/export_and_validation_W_B.py:518-542 (stage order,
+// layouts), models/ITA/QAT/ITA_softmax.py:51-61 (ITAmax), SURVEY.md App. A (integer spec).
+#pragma once
+#include <cuda.h>
+#include <stdlib.h>
+
+#include <type_traits>
+#include <vector>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace ita {
+
+constexpr int kS = 128;                 // rows per tile = tcgen05 M
+constexpr int kSlots = 2;
+constexpr int kEpiWarpsPerSlot = 8;
+constexpr int kWarpMma = kSlots * kEpiWarpsPerSlot;     // + slot
+constexpr int kWarpLoad = kWarpMma + kSlots;
+constexpr int kThreads = (kWarpLoad + 1) * 32;
+constexpr int kRegions = 4;             // accumulator ring per slot
+constexpr int kRegionCols = 64;
+constexpr int kTmemColsPerSlot = kRegions * kRegionCols;
+constexpr int kBarsPerSlot = 16;
+constexpr int kBiasK = 32;              // extra K columns carrying the bias digits
+constexpr int kBiasRadix = 127;
+constexpr int kOnesBytes = kS * kBiasK;
+
+enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2 };
+enum { STG_Q = 0, STG_K, STG_V, STG_S, STG_AV, STG_O };
+// per-slot mbarriers
+enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2, BAR_EMPTY = 6, BAR_DEP = 10 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */ };
+
+// Per-stage uniform requant parameters as the fused kernel consumes them.
+struct FRq {
+  int32_t multp;      // INT_HI: mult << (32 - shift);  INT_GEN: mult
+  int32_t shift;      // INT_GEN, and the 32-bit form of INT_HI
+  int32_t add;        // INT_GEN / TORCH
+  float eff;          // TORCH
+  long long c;        // INT_HI: (rnd << (32-shift)) + (add << 32);  INT_GEN: rnd
+  int32_t mult32;     // 32-bit form of INT_HI:  (acc * mult32 + c32) >> shift   (host-checked not to overflow)
+  int32_t c32;        //   rnd + (add << shift)
+};
+
+struct FusedParams {
+  const int8_t *wpanels;     // device: [Wq^T | Wk^T | Wv^T | Wo^T] (each with its bias-digit K columns) | constant A tile
+  int8_t *y;
+  long long batch;
+  int *abort_flag;
+  FRq rq[6];                 // Q K V QK AV O
+  // debug dump (natural layouts), any may be null
+  int8_t *dQ, *dK, *dV, *dA;
+  uint8_t *dAsm;
+  int8_t *dO;
+  long long *trace;          // developer builds (-DITA_TRACE): [warp][iteration < 8][chunk][4] SM clock stamps of CTA 0
+};
+
+template <int E, int P>
+struct Cfg {
+  static constexpr int S = kS;
+  static constexpr int NQ = P / 64;                                      // chunks per projection / per A.V
+  static constexpr int NCH = 4 * NQ + 4;                                 // chunks per frame
+  static constexpr int OC = E / 2;                                       // columns per output-projection chunk
+  static constexpr int WA_BYTES = P * (E + kBiasK);                      // each of Wq^T, Wk^T, Wv^T with bias digits
+  static constexpr int WO_BYTES = E * (P + kBiasK);                      // Wo^T with bias digits
+  static constexpr int OFF_W = 0;
+  static constexpr int OFF_ONES = 3 * WA_BYTES + WO_BYTES;
+  static constexpr int WPANEL_BYTES = OFF_ONES + kOnesBytes;             // what is bulk-copied at kernel start
+  static constexpr int X_BYTES = S * E;
+  static constexpr int SP_BYTES = S * P;
+  static constexpr int KA_BYTES = (S * P > S * S) ? S * P : S * S;       // K, later the softmax output
+  // the next frame's X tile lives in the part of the K buffer that the softmax output does not cover, when it fits and
+  // only the last K chunk overlaps it (that chunk's epilogue runs after the last MMA that reads X)
+  static constexpr bool X_IN_KTAIL = (S * S + X_BYTES <= KA_BYTES) && ((NQ - 1) * 64 * S <= S * S);
+  static constexpr int OFF_Q = 0, OFF_K = SP_BYTES, OFF_V = OFF_K + KA_BYTES;
+  static constexpr int OFF_X = X_IN_KTAIL ? OFF_K + S * S : OFF_V + SP_BYTES;
+  static constexpr int SLOT_BYTES = OFF_V + SP_BYTES + (X_IN_KTAIL ? 0 : X_BYTES);
+  static constexpr int OFF_SLOT = ((WPANEL_BYTES + 127) / 128) * 128;
+  static constexpr int OFF_XCHG = OFF_SLOT + kSlots * SLOT_BYTES;        // softmax pair exchange: [slot][2 halves][S] int2
+  static constexpr int XCHG_BYTES = kSlots * 2 * S * 8;
+  static constexpr int OFF_BAR = OFF_XCHG + XCHG_BYTES;
+  static constexpr int SMEM_BYTES = OFF_BAR + 512;
+  static_assert(E % 32 == 0 && P % 64 == 0, "E must be a multiple of 32 (tcgen05 kind::i8 K) and P of 64 (chunk width)");
+  static_assert(OC % 32 == 0 && OC <= kRegionCols, "output-projection chunks must be 32 or 64 columns");
+  static_assert(NCH % kRegions == 0, "chunks per frame must tile the accumulator ring");
+  static_assert((1 + kSlots * kBarsPerSlot) * 8 + 8 <= 512, "barrier area");
+  static_assert(WPANEL_BYTES % 16 == 0 && SLOT_BYTES % 128 == 0, "alignment");
+  // chunk c of a frame -> stage, index within the stage, first column, width
+  static constexpr int stage_of(int c) {
+    return c < NQ ? STG_Q : c < 2 * NQ ? STG_V : c < 3 * NQ ? STG_K : c < 3 * NQ + 2 ? STG_S : c < 4 * NQ + 2 ? STG_AV : STG_O;
+  }
+  static constexpr int idx_of(int c) {
+    return c < 3 * NQ ? c % NQ : c < 3 * NQ + 2 ? c - 3 * NQ : c < 4 * NQ + 2 ? c - 3 * NQ - 2 : c - 4 * NQ - 2;
+  }
+  static constexpr int ncols_of(int c) { return stage_of(c) == STG_O ? OC : 64; }
+  static constexpr int col0_of(int c) { return idx_of(c) * ncols_of(c); }
+  // which epilogue warpgroup of the slot drains chunk c: 0 = A (owns the logits), 1 = B
+  static constexpr int wg_of(int c) {
+    const int st = stage_of(c);
+    if (st == STG_S) return idx_of(c);                                   // keys 0..63 -> A, keys 64..127 -> B
+    if (c < 3 * NQ) return c % 2;                                        // projections: alternate
+    if (st == STG_AV) return idx_of(c) % 2;
+    return idx_of(c) == 0 ? 1 : 0;                                       // O0 -> B, O1 -> A
+  }
+  // arrivals (warps) that complete a stage's "operand written" barrier
+  static constexpr int dep_count(int stage) { return (stage == STG_S ? 2 : NQ) * 4; }
+  static constexpr int S0_CHUNK = 3 * NQ;
+  // The MMA thread needs region c%4 drained by its previous user p = c-4 (previous frame if negative).  The drain is
+  // implied when the thread has already waited for the "operand written" barrier of p's stage (the epilogue arrives
+  // there after its TMEM loads): Q/K at S0, V/S at AV0, AV at O0.  Output-projection chunks have no such barrier.
+  static constexpr int dep_wait_chunk(int stage) {
+    return (stage == STG_Q || stage == STG_K) ? 3 * NQ : (stage == STG_V || stage == STG_S) ? 3 * NQ + 2 : 4 * NQ + 2;
+  }
+  static constexpr bool needs_empty_wait(int c) {
+    const int p = (c + NCH - kRegions) % NCH;
+    const int sp = stage_of(p);
+    if (sp == STG_O) return true;
+    return p < c ? dep_wait_chunk(sp) > c : false;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------- requant forms
+// ALT selects how INT_HI elements are computed: 0 = one IMAD.HI each; 1 = 32-bit IMAD + SHF each; 2 = alternate (even
+// elements IMAD.HI, odd elements 32-bit) to balance the fma pipe (IMAD.HI occupies it twice as long) against issue slots.
+template <int MODE, int ALT>
+__device__ __forceinline__ int rq_apply(int acc, const FRq &r, int elem) {
+  if constexpr (MODE == RQM_INT_HI) {
+    if (ALT == 1 || (ALT == 2 && (elem & 1))) {
+      return (acc * r.mult32 + r.c32) >> r.shift;
+    } else {
+      // (acc*mult + rnd) >> shift + add  ==  hi32( acc * (mult << (32-shift)) + c ),  c folded on the host
+      long long p = (long long)acc * (long long)r.multp + r.c;
+      return (int)(p >> 32);
+    }
+  } else if constexpr (MODE == RQM_INT_GEN) {
+    long long p = (long long)acc * (long long)r.multp + r.c;
+    return (int)(p >> r.shift) + r.add;
+  } else {
+    float f = __fmul_rn(__int2float_rn(acc), r.eff);
+    return __float2int_rn(f) + r.add;
+  }
+}
+
+__device__ __forceinline__ uint32_t pack_s8x4(int y0, int y1, int y2, int y3) {
+  uint32_t t, d;
+  asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(y3), "r"(y2), "r"(0));
+  asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(y1), "r"(y0), "r"(t));
+  return d;
+}
+__device__ __forceinline__ uint32_t pack_u8x4(int y0, int y1, int y2, int y3) {
+  uint32_t t, d;
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(y3), "r"(y2), "r"(0));
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(y1), "r"(y0), "r"(t));
+  return d;
+}
+// X tile [kS rows x E bytes] -> panel layout: one 2-D TMA box (16 B x kS rows) per 16-byte column chunk
+template <int E>
+__device__ __forceinline__ void load_x_tile(void *dst, const CUtensorMap *map, long long frame, uint64_t *bar) {
+  mbar_arrive_expect_tx(bar, kS * E);
+#pragma unroll
+  for (int c = 0; c < E / 16; ++c) tma_load_2d(reinterpret_cast<uint8_t *>(dst) + c * kS * 16, map, c * 16, (int)(frame * kS), bar);
+}
+
+__device__ __forceinline__ uint32_t shr_clamp(uint32_t v, uint32_t s) {   // PTX shr: shift amounts > 31 give 0
+  uint32_t r;
+  asm("shr.u32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(s));
+  return r;
+}
+
+#ifdef ITA_TRACE
+#define ITA_TR(prm, warp, it, c, k)                                                                             \
+  do {                                                                                                          \
+    if ((prm).trace && blockIdx.x == 0 && (it) < 8 && (threadIdx.x & 31) == 0)                                   \
+      (prm).trace[((((long long)(warp)) * 8 + (it)) * 32 + (c)) * 4 + (k)] = clock64();                          \
+  } while (0)
+#else
+#define ITA_TR(prm, warp, it, c, k) do { } while (0)
+#endif
+
+// compile-time loop
+template <int I, int N, class F>
+__device__ __forceinline__ void static_for(F &&f) {
+  if constexpr (I < N) {
+    f(std::integral_constant<int, I>{});
+    static_for<I + 1, N>(f);
+  }
+}
+
+// tcgen05.wait::ld that also "redefines" the 32 destination registers of the load it waits for, so that the compiler
+// cannot move or copy them between the asynchronous load and the wait.
+__device__ __forceinline__ void tmem_wait32(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                 "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]),
+                 "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]),
+                 "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
+
+// Empty asm that "redefines" 32 registers: an ordering point for the compiler, no instruction.
+__device__ __forceinline__ void tmem_pin32(uint32_t (&v)[32]) {
+  asm volatile(""
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                 "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]),
+                 "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]),
+                 "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
+
+// Walk NG groups of 32 accumulator columns of this thread's row, software-pipelined: the TMEM load of group g+1 is in
+// flight while f(g, v) works on group g.  addr(g) gives the TMEM address of group g.  After the last load has landed,
+// `done()` runs once (used to hand the TMEM region back to the MMA thread).
+template <int NG, class A, class F, class D>
+__device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
+  uint32_t va[32], vb[32];
+  tmem_ld32(addr(0), va);
+  tmem_wait32(va);
+  static_for<0, NG>([&](auto gg) {
+    constexpr int g = decltype(gg)::value;
+    uint32_t(&cur)[32] = (g & 1) ? vb : va;
+    uint32_t(&nxt)[32] = (g & 1) ? va : vb;
+    if constexpr (g + 1 < NG) {
+      tmem_ld32(addr(g + 1), nxt);
+      tmem_pin32(cur);              // keeps the compiler from hoisting the work on `cur` above the load just issued
+    }
+    if constexpr (g + 1 == NG) done();
+    f(gg, cur);
+    if constexpr (g + 1 < NG) tmem_wait32(nxt);
+  });
+}
+
+// Requantise 32 accumulators of one row -> int8 -> panel buffer (and/or global).
+//   panel      shared-memory panel buffer of a [kS x *] matrix (nullptr: do not store to smem)
+//   col        first of the 32 columns inside that matrix
+//   grow       global pointer to the first of these 32 columns (natural layout) or nullptr
+template <int MODE, int ALT>
+__device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const FRq &r, int8_t *panel, int row, int col, int8_t *grow) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 16) {
+    uint32_t w[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      int y[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) y[i] = rq_apply<MODE, ALT>((int)v[j + q * 4 + i], r, i);
+      w[q] = pack_s8x4(y[0], y[1], y[2], y[3]);
+    }
+    const uint4 o = make_uint4(w[0], w[1], w[2], w[3]);
+    if (panel) *reinterpret_cast<uint4 *>(panel + ((col + j) >> 4) * (kS * 16) + row * 16) = o;
+    if (grow) *reinterpret_cast<uint4 *>(grow + j) = o;
+  }
+}
+
+struct SlotCtx {
+  uint64_t *bars;       // this slot's kBarsPerSlot mbarriers
+  uint8_t *smem;        // this slot's operand buffers: Q(O) | K(Asm, next X) | V | [X]
+  uint32_t tmem;        // first TMEM column of this slot's accumulator ring
+};
+
+// ---------------------------------------------------------------------------------------------------- ITAmax on a row
+// A row of the logits accumulator is 128 columns in two TMEM regions; the thread of warpgroup A that owns the row's
+// TMEM lane works on keys 0..63 (HALF 0), its twin in warpgroup B (same lane quadrant, same lane) on keys 64..127.
+// The two warps of such a pair exchange their partial row max / row sum through shared memory (`xch`: [2 halves][128
+// rows] of {max, sum}) and meet at a 64-thread named barrier.  The half row is read from TMEM up to three times
+// instead of being kept in registers; `release()` runs when the last read has landed.  Writes the u8 probabilities
+// into the K buffer (A operand of A.V) and, for DUMP, to global memory.
+struct PairCtx {
+  uint32_t bar_id;     // named barrier shared by the two warps of the pair (64 threads)
+  int2 *xch;           // this slot's exchange area [2][kS]
+};
+__device__ __forceinline__ void pair_sync(const PairCtx &pc) { named_bar_sync(pc.bar_id, 64); }
+
+// repo_global (models/ITA/QAT/ITA_softmax.py:51-61): m = row max, d = m - a, n = 256 >> d, inv = floor(255*2^16 / sum n),
+// out = (n * inv) >> 16 == (inv >> 8) >> d.  Requantisation is monotone, so the row max is taken on the raw
+// accumulators (pass 1) and requantised once.  Passes 2 and 3 need d only; for INT_HI it comes out of a single
+// multiply-add,  d = hi32(acc * -multp + c2),  c2 = (m << 32) - c + 2^32 - 1   (-floor(z / 2^32) == floor((-z + 2^32 - 1) / 2^32)),
+// which ignores the s8 saturation of a.  That is exact whenever no logit of the row saturates high (unsaturated max
+// <= 127) and low saturation cannot matter (m >= -119: a saturated element has d > 8 either way); other rows (and
+// the other requant forms) take the general form with the explicit clamp.  The choice is made per warp; both warps of
+// a pair hold the same rows and therefore choose alike.
+template <int MODE, int ALT, bool DUMP, int HALF, class R>
+__device__ __forceinline__ void itamax_repo_half(uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
+                                                 const PairCtx &pc, R &&release) {
+  auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
+  int2 *mine = pc.xch + HALF * kS + row, *other = pc.xch + (HALF ^ 1) * kS + row;
+  // ---- pass 1: max of the raw accumulators
+  int amax = (int)0x80000000;
+  tmem_walk<2>(addr,
+               [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                 for (int i = 0; i < 32; ++i) amax = max(amax, (int)v[i]);
+               },
+               [] {});
+  mine->x = amax;
+  pair_sync(pc);
+  amax = max(amax, other->x);
+  const int m_un = rq_apply<MODE, 0>(amax, rq, 0);
+  const int m = min(max(m_un, -128), 127);
+  bool fast = false;
+  if constexpr (MODE == RQM_INT_HI && !DUMP) fast = __all_sync(0xffffffffu, m_un <= 127 && m >= -119);
+  uint32_t sum = 0;
+  if (fast) {
+    const long long c2 = ((long long)m << 32) - rq.c + 0xFFFFFFFFLL;
+    const int nmultp = -rq.multp;
+    const int nmult32 = -rq.mult32;
+    const int c32n = m * (int)(1u << rq.shift) - rq.c32 + (int)((1u << rq.shift) - 1u);
+    auto dist = [&](int acc, int elem) -> uint32_t {
+      if (ALT == 1 || (ALT == 2 && (elem & 1))) return (uint32_t)((acc * nmult32 + c32n) >> rq.shift);
+      return (uint32_t)(((long long)acc * (long long)nmultp + c2) >> 32);
+    };
+    tmem_walk<2>(addr,
+                 [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                   for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist((int)v[i], i));
+                 },
+                 [] {});
+    mine->y = (int)sum;
+    pair_sync(pc);
+    sum += (uint32_t)other->y;
+    const uint32_t inv8 = ((255u * 65536u) / sum) >> 8;
+    tmem_walk<2>(addr,
+                 [&](auto gg, const uint32_t(&v)[32]) {
+                   constexpr int g = decltype(gg)::value;
+#pragma unroll
+                   for (int j = 0; j < 32; j += 16) {
+                     uint32_t w[4];
+#pragma unroll
+                     for (int q = 0; q < 4; ++q) {
+                       int o[4];
+#pragma unroll
+                       for (int i = 0; i < 4; ++i) o[i] = (int)shr_clamp(inv8, dist((int)v[j + q * 4 + i], i));
+                       w[q] = pack_u8x4(o[0], o[1], o[2], o[3]);
+                     }
+                     *reinterpret_cast<uint4 *>(k_buf + ((HALF * 64 + g * 32 + j) >> 4) * (kS * 16) + row * 16) =
+                         make_uint4(w[0], w[1], w[2], w[3]);
+                   }
+                 },
+                 release);
+  } else {
+    auto dist = [&](int acc) -> uint32_t {
+      const int a = min(max(rq_apply<MODE, 0>(acc, rq, 0), -128), 127);
+      return (uint32_t)(m - a);
+    };
+    tmem_walk<2>(addr,
+                 [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                   for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist((int)v[i]));
+                 },
+                 [] {});
+    mine->y = (int)sum;
+    pair_sync(pc);
+    sum += (uint32_t)other->y;
+    const uint32_t inv8 = ((255u * 65536u) / sum) >> 8;
+    tmem_walk<2>(addr,
+                 [&](auto gg, const uint32_t(&v)[32]) {
+                   constexpr int g = decltype(gg)::value;
+#pragma unroll
+                   for (int j = 0; j < 32; j += 16) {
+                     uint32_t w[4], wa[4];
+#pragma unroll
+                     for (int q = 0; q < 4; ++q) {
+                       int o[4], a[4];
+#pragma unroll
+                       for (int i = 0; i < 4; ++i) {
+                         const uint32_t d = dist((int)v[j + q * 4 + i]);
+                         o[i] = (int)shr_clamp(inv8, d);
+                         a[i] = m - (int)d;
+                       }
+                       w[q] = pack_u8x4(o[0], o[1], o[2], o[3]);
+                       if constexpr (DUMP) wa[q] = pack_s8x4(a[0], a[1], a[2], a[3]);
+                     }
+                     const uint4 ov = make_uint4(w[0], w[1], w[2], w[3]);
+                     *reinterpret_cast<uint4 *>(k_buf + ((HALF * 64 + g * 32 + j) >> 4) * (kS * 16) + row * 16) = ov;
+                     if constexpr (DUMP) {
+                       if (gAsm) *reinterpret_cast<uint4 *>(gAsm + HALF * 64 + g * 32 + j) = ov;
+                       if (gA) *reinterpret_cast<uint4 *>(gA + HALF * 64 + g * 32 + j) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
+                     }
+                   }
+                 },
+                 release);
+  }
+  // (the exchange area needs no closing barrier: a value is overwritten only after a later pair_sync that the partner
+  //  reaches after its read of the old value)
+}
+
+// Recalled golden-model streaming softmax (oracle/ita_ref.py itamax_stream16): 16-column groups in
+// column order, running max m and denominator, eps = 1/32 with round-half-up; then out = inv >> rhu((m - a) / 32).
+// The row is walked in column order: HALF 1 continues from the state HALF 0 publishes.
+template <int MODE, bool DUMP, int HALF, class R>
+__device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
+                                                   const PairCtx &pc, R &&release) {
+  auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
+  auto biased = [&](uint32_t acc) -> uint32_t {   // sat8(requant) + 128 in [0, 255]
+    return (uint32_t)(min(max(rq_apply<MODE, 0>((int)acc, rq, 0), -128), 127) + 128);
+  };
+  int2 *st0 = pc.xch + row, *st1 = pc.xch + kS + row;
+  uint32_t m = 0, tot = 0;
+  if constexpr (HALF == 1) {
+    pair_sync(pc);                 // HALF 0 has published its running state
+    m = (uint32_t)st0->x;
+    tot = (uint32_t)st0->y;
+  }
+  tmem_walk<2>(addr,
+               [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                 for (int h = 0; h < 2; ++h) {
+                   uint32_t b[16];
+                   uint32_t cm = 0;
+#pragma unroll
+                   for (int i = 0; i < 16; ++i) {
+                     b[i] = biased(v[h * 16 + i]);
+                     cm = max(cm, b[i]);
+                   }
+                   if (cm > m) {
+                     tot = shr_clamp(tot, (cm - m + 16) >> 5);
+                     m = cm;
+                   }
+#pragma unroll
+                   for (int i = 0; i < 16; ++i) tot += 256u >> ((m - b[i] + 16) >> 5);
+                 }
+               },
+               [] {});
+  if constexpr (HALF == 0) {
+    *st0 = make_int2((int)m, (int)tot);
+    pair_sync(pc);
+    pair_sync(pc);                 // HALF 1 has published the final state
+    m = (uint32_t)st1->x;
+    tot = (uint32_t)st1->y;
+  } else {
+    *st1 = make_int2((int)m, (int)tot);
+    pair_sync(pc);
+  }
+  const uint32_t inv = (255u * 256u) / (tot < 1 ? 1 : tot);
+  tmem_walk<2>(addr,
+               [&](auto gg, const uint32_t(&v)[32]) {
+                 constexpr int g = decltype(gg)::value;
+#pragma unroll
+                 for (int j = 0; j < 32; j += 16) {
+                   uint32_t w[4], wa[4];
+#pragma unroll
+                   for (int q = 0; q < 4; ++q) {
+                     int o[4], a[4];
+#pragma unroll
+                     for (int i = 0; i < 4; ++i) {
+                       const uint32_t b = biased(v[j + q * 4 + i]);
+                       o[i] = (int)(inv >> ((m - b + 16) >> 5));
+                       a[i] = (int)b - 128;
+                     }
+                     w[q] = pack_u8x4(o[0], o[1], o[2], o[3]);
+                     if constexpr (DUMP) wa[q] = pack_s8x4(a[0], a[1], a[2], a[3]);
+                   }
+                   const uint4 ov = make_uint4(w[0], w[1], w[2], w[3]);
+                   *reinterpret_cast<uint4 *>(k_buf + ((HALF * 64 + g * 32 + j) >> 4) * (kS * 16) + row * 16) = ov;
+                   if constexpr (DUMP) {
+                     if (gAsm) *reinterpret_cast<uint4 *>(gAsm + HALF * 64 + g * 32 + j) = ov;
+                     if (gA) *reinterpret_cast<uint4 *>(gA + HALF * 64 + g * 32 + j) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
+                   }
+                 }
+               },
+               release);
+}
+
+// ---------------------------------------------------------------------------------------------------- epilogue warps
+// One warpgroup (WG = 0: "A", 1: "B") of one slot: drains the chunks Cfg::wg_of assigns to it, in chunk order.  The chunk
+// schedule is unrolled at compile time: a lone warp issues one dependent instruction every ~5 cycles, so run-time chunk
+// bookkeeping (tried: a run-time loop over three code paths) costs more than the instruction-cache misses it saves.
+template <int E, int P, int MODE, int SOFTMAX, int ALT, bool DUMP, int WG>
+__device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const SlotCtx &sc, const PairCtx &pc, int quad, int lane, long long iters,
+                                              long long frame0, long long frame_stride) {
+  using C = Cfg<E, P>;
+  const int row = quad * 32 + lane;
+  const uint32_t t_lane = sc.tmem + ((uint32_t)(quad * 32) << 16);
+  int8_t *const q_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_Q, *const k_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_K,
+               *const v_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_V;
+  bool ok = true;
+  for (long long it = 0; it < iters && ok; ++it) {
+    const long long f = frame0 + it * frame_stride;
+    static_for<0, C::NCH>([&](auto cc) {
+      constexpr int c = decltype(cc)::value;
+      constexpr int stage = C::stage_of(c), idx = C::idx_of(c), NC = C::ncols_of(c), col0 = C::col0_of(c), r = c % kRegions;
+      if constexpr (C::wg_of(c) == WG) {
+        if (!ok) return;
+        const uint32_t use = (uint32_t)(it * (C::NCH / kRegions)) + c / kRegions;
+        ITA_TR(prm, threadIdx.x >> 5, it, c, 0);
+        ok = mbar_wait(sc.bars + BAR_FULL + r, use & 1, prm.abort_flag);
+        if (!ok) return;
+        ITA_TR(prm, threadIdx.x >> 5, it, c, 1);
+        tc_fence_after();
+        const uint32_t taddr = t_lane + r * kRegionCols;
+        auto release = [&] {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(sc.bars + BAR_EMPTY + r);
+          ITA_TR(prm, threadIdx.x >> 5, it, c, 2);
+        };
+        if constexpr (stage == STG_S) {
+          // ---- logits: this warpgroup's 64 key columns -> ITAmax -> Asm (u8) into the K buffer
+          int8_t *gA = nullptr;
+          uint8_t *gAsm = nullptr;
+          if constexpr (DUMP) {
+            if (prm.dA) gA = prm.dA + (f * kS + row) * kS;
+            if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
+          }
+          if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
+            itamax_repo_half<MODE, ALT, DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+          else
+            itamax_stream_half<MODE, DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+        } else {
+          int8_t *panel = stage == STG_Q ? q_buf : stage == STG_K ? k_buf : stage == STG_V ? v_buf : stage == STG_AV ? q_buf : nullptr;
+          int8_t *g = nullptr;
+          if constexpr (stage == STG_O) {
+            g = prm.y + (f * kS + row) * E + col0;
+          } else if constexpr (DUMP) {
+            int8_t *base = stage == STG_Q ? prm.dQ : stage == STG_K ? prm.dK : stage == STG_V ? prm.dV : prm.dO;
+            if (base) g = base + (f * kS + row) * P + col0;
+          }
+          tmem_walk<NC / 32>([&](int gi) { return taddr + (uint32_t)gi * 32u; },
+                             [&](auto gg, const uint32_t(&v)[32]) {
+                               constexpr int gi = decltype(gg)::value;
+                               requant_store32<MODE, ALT>(v, prm.rq[stage], panel, row, col0 + gi * 32, g ? g + gi * 32 : nullptr);
+                             },
+                             release);
+        }
+        if constexpr (stage != STG_O) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(sc.bars + BAR_DEP + stage);
+        }
+        ITA_TR(prm, threadIdx.x >> 5, it, c, 3);
+      }
+    });
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------- the kernel
+template <int E, int P, int MODE, int SOFTMAX, int ALT, bool DUMP>
+__global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant__ CUtensorMap xmap, const FusedParams prm) {
+  using C = Cfg<E, P>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + C::OFF_BAR);
+  uint64_t *bar_w = bars;                          // weights + constant tile landed
+  uint64_t *slot_bars = bars + 1;                  // [slot][kBarsPerSlot]
+  uint32_t *s_tmem = reinterpret_cast<uint32_t *>(bars + 1 + kSlots * kBarsPerSlot);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long nframes = prm.batch;
+  // frame f of slot s in iteration it:  f = (it * gridDim.x + blockIdx.x) * kSlots + s
+  const long long frame_stride = (long long)gridDim.x * kSlots;
+  auto iters_of = [&](int slot) -> long long {
+    long long first = (long long)blockIdx.x * kSlots + slot;
+    if (first >= nframes) return 0;
+    return (nframes - first + frame_stride - 1) / frame_stride;
+  };
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar_w, 1);
+    for (int s = 0; s < kSlots; ++s) {
+      uint64_t *b = slot_bars + s * kBarsPerSlot;
+      mbar_init(b + BAR_X, 1);
+      mbar_init(b + BAR_XFREE, 1);
+      for (int r = 0; r < kRegions; ++r) {
+        mbar_init(b + BAR_FULL + r, 1);
+        mbar_init(b + BAR_EMPTY + r, 4);
+      }
+      for (int st = STG_Q; st <= STG_AV; ++st) mbar_init(b + BAR_DEP + st, C::dep_count(st));
+    }
+    fence_mbar_init();
+  }
+  if (warp == kWarpLoad) tmem_alloc<512>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == kWarpLoad) {
+    // ================================================================= loader: weights once, then the X tiles
+    if (lane == 0) {
+      tma_prefetch_desc(&xmap);
+      mbar_arrive_expect_tx(bar_w, C::WPANEL_BYTES);
+      bulk_g2s(smem + C::OFF_W, prm.wpanels, C::WPANEL_BYTES, bar_w);
+      long long iters[kSlots];
+      long long mx = 0;
+      for (int s = 0; s < kSlots; ++s) {
+        iters[s] = iters_of(s);
+        mx = iters[s] > mx ? iters[s] : mx;
+        if (iters[s] > 0)
+          load_x_tile<E>(smem + C::OFF_SLOT + s * C::SLOT_BYTES + C::OFF_X, &xmap, (long long)blockIdx.x * kSlots + s,
+                         slot_bars + s * kBarsPerSlot + BAR_X);
+      }
+      bool ok = true;
+      for (long long it = 0; it + 1 < mx && ok; ++it)
+        for (int s = 0; s < kSlots && ok; ++s)
+          if (it + 1 < iters[s]) {
+            // every MMA of frame `it` that reads this slot's X tile (or the K columns it shares storage with) is complete
+            ok = mbar_wait(slot_bars + s * kBarsPerSlot + BAR_XFREE, (uint32_t)(it & 1), prm.abort_flag);
+            if (ok)
+              load_x_tile<E>(smem + C::OFF_SLOT + s * C::SLOT_BYTES + C::OFF_X, &xmap,
+                             (long long)blockIdx.x * kSlots + s + (it + 1) * frame_stride, slot_bars + s * kBarsPerSlot + BAR_X);
+          }
+    }
+    __syncwarp();
+  } else if (warp >= kWarpMma) {
+    // ================================================================= MMA issue for one slot
+    // The whole warp walks the chunk schedule (barrier waits and operand addresses stay warp-uniform, so they live
+    // in the uniform datapath); one elected lane issues the tcgen05.mma / commit instructions.
+    const int slot = __shfl_sync(0xffffffffu, warp - kWarpMma, 0);
+    const long long iters = iters_of(slot);
+    if (iters > 0) {
+      const bool leader = elect_one();
+      uint64_t *b = slot_bars + slot * kBarsPerSlot;
+      bool ok = mbar_wait(bar_w, 0, prm.abort_flag);
+      // instruction descriptors (M = 128)
+      constexpr uint32_t ID_PROJ = make_idesc_i8(kS, 64, 1, 1, 0, 0);      // X . W^T           64 of the P columns
+      constexpr uint32_t ID_QK = make_idesc_i8(kS, 64, 1, 1, 0, 0);        // Q . K^T           64 key columns
+      constexpr uint32_t ID_AV = make_idesc_i8(kS, 64, 0, 1, 0, 1);        // Asm(u8) . V       64 of the P columns, B MN-major
+      constexpr uint32_t ID_O = make_idesc_i8(kS, C::OC, 1, 1, 0, 0);      // O . Wo            E/2 columns
+      // operand buffer addresses in 16-byte units (the descriptor address field)
+      const uint32_t w16 = smem_u32(smem + C::OFF_W) >> 4;
+      const uint32_t ones16 = smem_u32(smem + C::OFF_ONES) >> 4;
+      const uint32_t slot16 = smem_u32(smem + C::OFF_SLOT + slot * C::SLOT_BYTES) >> 4;
+      const uint32_t x16 = slot16 + (C::OFF_X >> 4), q16 = slot16 + (C::OFF_Q >> 4), k16 = slot16 + (C::OFF_K >> 4),
+                     v16 = slot16 + (C::OFF_V >> 4);
+      const uint32_t d_base = tmem_base + slot * kTmemColsPerSlot;
+      for (long long it = 0; it < iters && ok; ++it) {
+        const uint32_t ph = (uint32_t)(it & 1);
+        static_for<0, C::NCH>([&](auto cc) {
+          constexpr int c = decltype(cc)::value;
+          constexpr int stage = C::stage_of(c), idx = C::idx_of(c), r = c % kRegions;
+          if (!ok) return;
+          const uint32_t use = (uint32_t)(it * (C::NCH / kRegions)) + c / kRegions;
+          ITA_TR(prm, warp, it, c, 0);
+          if constexpr (C::needs_empty_wait(c)) {
+            if (use > 0) ok = mbar_wait(b + BAR_EMPTY + r, (use - 1) & 1, prm.abort_flag);
+          }
+          ITA_TR(prm, warp, it, c, 1);
+          if constexpr (idx == 0) {
+            if constexpr (stage == STG_Q) ok = ok && mbar_wait(b + BAR_X, ph, prm.abort_flag);
+            if constexpr (stage == STG_S) ok = ok && mbar_wait(b + BAR_DEP + STG_Q, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_K, ph, prm.abort_flag);
+            if constexpr (stage == STG_AV) ok = ok && mbar_wait(b + BAR_DEP + STG_V, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_S, ph, prm.abort_flag);
+            if constexpr (stage == STG_O) ok = ok && mbar_wait(b + BAR_DEP + STG_AV, ph, prm.abort_flag);
+          }
+          if (!ok) return;
+          tc_fence_after();
+          ITA_TR(prm, warp, it, c, 2);
+          const uint32_t d_tmem = d_base + r * kRegionCols;
+          if (leader) {
+            if constexpr (stage <= STG_V) {
+              // projections: A = X [S rows, K = E] K-major; B = rows [64 idx, +64) of W_t^T [P rows, K = E + 32] K-major;
+              // the last K step multiplies the constant tile with the bias digits
+              constexpr uint32_t wt = stage * C::WA_BYTES + idx * 64 * 16;
+#pragma unroll
+              for (int k = 0; k < E / 32; ++k)
+                umma_i8(d_tmem, make_smem_desc_rel(x16, k * 2 * kS * 16, kS * 16, 128),
+                        make_smem_desc_rel(w16, wt + k * 2 * P * 16, P * 16, 128), ID_PROJ, k > 0);
+              umma_i8(d_tmem, make_smem_desc_rel(ones16, 0, kS * 16, 128), make_smem_desc_rel(w16, wt + (E / 16) * P * 16, P * 16, 128),
+                      ID_PROJ, 1);
+            } else if constexpr (stage == STG_S) {
+              // logits: A = Q [S, K = P] K-major; B = rows (keys) [64 idx, +64) of K [S rows, K = P] K-major
+#pragma unroll
+              for (int k = 0; k < P / 32; ++k)
+                umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128),
+                        make_smem_desc_rel(k16, idx * 64 * 16 + k * 2 * kS * 16, kS * 16, 128), ID_QK, k > 0);
+            } else if constexpr (stage == STG_AV) {
+              // context: A = Asm [S, K = S] u8 K-major (in the K buffer); B = columns [64 idx, +64) of V [K = S rows, N = P] MN-major
+#pragma unroll
+              for (int k = 0; k < kS / 32; ++k)
+                umma_i8(d_tmem, make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128),
+                        make_smem_desc_rel(v16, idx * 4 * kS * 16 + k * 32 * 16, 128, kS * 16), ID_AV, k > 0);
+            } else {
+              // output projection: A = O [S, K = P] K-major (in the Q buffer); B = rows [OC idx, +OC) of Wo^T [E rows, K = P + 32]
+              constexpr uint32_t wo = 3 * C::WA_BYTES + idx * C::OC * 16;
+#pragma unroll
+              for (int k = 0; k < P / 32; ++k)
+                umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128), make_smem_desc_rel(w16, wo + k * 2 * E * 16, E * 16, 128),
+                        ID_O, k > 0);
+              umma_i8(d_tmem, make_smem_desc_rel(ones16, 0, kS * 16, 128), make_smem_desc_rel(w16, wo + (P / 16) * E * 16, E * 16, 128), ID_O, 1);
+            }
+            umma_commit(b + BAR_FULL + r);
+            // the X buffer may be overwritten once its last reader is complete: the last projection, or -- when X shares
+            // storage with the K columns beyond the softmax output -- the last logits MMA
+            if constexpr (C::X_IN_KTAIL ? (stage == STG_S && idx == 1) : (c == 3 * C::NQ - 1)) umma_commit(b + BAR_XFREE);
+          }
+          __syncwarp();
+          ITA_TR(prm, warp, it, c, 3);
+        });
+      }
+    }
+  } else {
+    // ================================================================= epilogue warps
+    const int slot = warp / kEpiWarpsPerSlot;
+    const int quad = warp & 3;
+    const int wg = (warp >> 2) & 1;
+    SlotCtx sc;
+    sc.bars = slot_bars + slot * kBarsPerSlot;
+    sc.smem = smem + C::OFF_SLOT + slot * C::SLOT_BYTES;
+    sc.tmem = tmem_base + slot * kTmemColsPerSlot;
+    PairCtx pc;
+    pc.bar_id = 1 + slot * 4 + quad;
+    pc.xch = reinterpret_cast<int2 *>(smem + C::OFF_XCHG) + slot * 2 * kS;
+    const long long iters = iters_of(slot);
+    if (iters > 0) {
+      const long long frame0 = (long long)blockIdx.x * kSlots + slot;
+      if (wg == 0)
+        epilogue_loop<E, P, MODE, SOFTMAX, ALT, DUMP, 0>(prm, sc, pc, quad, lane, iters, frame0, frame_stride);
+      else
+        epilogue_loop<E, P, MODE, SOFTMAX, ALT, DUMP, 1>(prm, sc, pc, quad, lane, iters, frame0, frame_stride);
+    }
+  }
+
+  // ---- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWarpLoad) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------- instantiation
+typedef void (*KernelFn)(const CUtensorMap, const FusedParams);
+
+// One translation unit per (E, P) shape defines these (ITA_FUSED_DEFINE_SHAPE) so that the shapes compile in parallel.
+struct FusedShape {
+  int E, P, smem_bytes;
+  // mode: RQM_*; softmax: ITA_SOFTMAX_*; alt: INT_HI element form (0 / 1 / 2); dump: intermediates to global
+  KernelFn (*pick)(int mode, int softmax, int alt, bool dump);
+};
+
+#ifdef ITA_FUSED_ALL_ALT
+#define ITA_FUSED_ALT1(E, P, SM) if (mode == RQM_INT_HI && softmax == SM && alt == 1 && !dump) return k_ita_fused<E, P, RQM_INT_HI, SM, 1, false>;
+#else
+#define ITA_FUSED_ALT1(E, P, SM)
+#endif
+
+#define ITA_FUSED_PICK_SM(E, P, SM)                                                                                   \
+  if (mode == RQM_INT_HI && softmax == SM && alt == 2 && !dump) return k_ita_fused<E, P, RQM_INT_HI, SM, 2, false>;   \
+  ITA_FUSED_ALT1(E, P, SM)                                                                                            \
+  if (mode == RQM_INT_HI && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_HI, SM, 0, true> : k_ita_fused<E, P, RQM_INT_HI, SM, 0, false>;     \
+  if (mode == RQM_INT_GEN && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_GEN, SM, 0, true> : k_ita_fused<E, P, RQM_INT_GEN, SM, 0, false>; \
+  if (mode == RQM_TORCH && softmax == SM) return dump ? k_ita_fused<E, P, RQM_TORCH, SM, 0, true> : k_ita_fused<E, P, RQM_TORCH, SM, 0, false>;
+
+#define ITA_FUSED_DEFINE_SHAPE(E, P)                                              \
+  static KernelFn pick_##E##_##P(int mode, int softmax, int alt, bool dump) {     \
+    ITA_FUSED_PICK_SM(E, P, 0)                                                    \
+    ITA_FUSED_PICK_SM(E, P, 1)                                                    \
+    return nullptr;                                                               \
+  }                                                                               \
+  extern const FusedShape fused_shape_##E##_##P = {E, P, Cfg<E, P>::SMEM_BYTES, pick_##E##_##P};
+
+}  // namespace ita

@@ -38,8 +38,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: every spin loop in this library gives up after ~2 s of SM clock and raises `*abort_flag` (a device int the
-// host checks after the launch), so that a protocol bug shows up as an error code instead of a hung GPU.
+// Bounded wait.  The loop itself is four instructions (try_wait suspends the thread in hardware for a while when the
+// phase is not complete); it gives up after kWaitSpinLimit failed polls and raises `*abort_flag` (a device int the host
+// checks after the launch), so that a protocol bug shows up as an error code instead of a hung GPU.
+constexpr uint32_t kWaitSpinLimit = 1u << 24;
+#ifdef ITA_OLD_WAIT
 __device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *abort_flag) {
   if (mbar_try_wait(bar, parity)) return true;
   const long long t0 = clock64();
@@ -54,6 +57,39 @@ __device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *a
   }
   return true;
 }
+#else
+__device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *abort_flag) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      ".reg .u32 n;\n\t"
+      "mov.u32 n, 0;\n"
+      "ITA_WAIT_%=:\n\t"
+#ifdef ITA_WAIT_HINT_NS
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %4;\n\t"
+#else
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+#endif
+      "@p bra ITA_DONE_%=;\n\t"
+      "add.u32 n, n, 1;\n\t"
+      "setp.lt.u32 q, n, %3;\n\t"
+      "@q bra ITA_WAIT_%=;\n"
+      "ITA_DONE_%=:\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(ok)
+#ifdef ITA_WAIT_HINT_NS
+      : "r"(smem_u32(bar)), "r"(parity), "r"(kWaitSpinLimit), "r"((uint32_t)ITA_WAIT_HINT_NS)
+#else
+      : "r"(smem_u32(bar)), "r"(parity), "r"(kWaitSpinLimit)
+#endif
+      : "memory");
+  if (ok) return true;
+  atomicExch(abort_flag, 1);
+  return false;
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------------- proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
@@ -153,6 +189,16 @@ __host__ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, 
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;  // descriptor version for sm_100
+  return d;
+}
+// The same descriptor for an operand at `base16 * 16 + off_bytes`, where base16 = (shared address of a 16-byte aligned
+// buffer) >> 4: with compile-time off/LBO/SBO this is one 32-bit add and a constant high word (shared memory is
+// < 256 KB, so the 14-bit address field cannot carry into the LBO field).
+__device__ __forceinline__ uint64_t make_smem_desc_rel(uint32_t base16, uint32_t off_bytes, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  const uint32_t lo = base16 + ((off_bytes >> 4) | ((lbo_bytes >> 4) << 16));
+  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14);
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
   return d;
 }
 // Instruction descriptor for kind::i8 (dense, s32 accumulate).  a_signed/b_signed: 1 = s8, 0 = u8; *_mn_major: 1 = the operand

@@ -126,6 +126,47 @@ __global__ void __launch_bounds__(128) k_umma_peak(int iters, int *abort_flag) {
   }
 }
 
+
+// TMEM -> register read bandwidth: `nw` warps of one CTA (warp w reads lane quadrant w%4) loop over 32x32b.x32 loads
+// (4 KB per load per warp) with `depth` loads in flight per warp.  cycles[blockIdx.x] = SM clocks for the whole loop.
+__global__ void __launch_bounds__(512) k_tmem_read(int iters, int nw, int depth, long long *cycles, int *sink) {
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  if (warp == 0) tmem_alloc<512>(&s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem + ((uint32_t)((warp & 3) * 32) << 16);
+  uint32_t acc = 0;
+  long long t0 = clock64();
+  if (warp < nw) {
+    uint32_t v0[32], v1[32], v2[32], v3[32];
+    for (int it = 0; it < iters; ++it) {
+      const uint32_t col = (uint32_t)((it * 4 + warp / 4) * 32) & 511u;
+      tmem_ld32(tmem + col, v0);
+      if (depth >= 2) tmem_ld32(tmem + ((col + 32) & 511u), v1);
+      if (depth >= 4) {
+        tmem_ld32(tmem + ((col + 64) & 511u), v2);
+        tmem_ld32(tmem + ((col + 96) & 511u), v3);
+      }
+      tmem_ld_wait();
+      acc += v0[0] ^ v0[31];
+      if (depth >= 2) acc += v1[1] ^ v1[30];
+      if (depth >= 4) acc += (v2[2] ^ v2[29]) + (v3[3] ^ v3[28]);
+    }
+  }
+  __syncthreads();
+  long long t1 = clock64();
+  if (tid == 0) cycles[blockIdx.x] = t1 - t0;
+  if (acc == 0x12345678u) sink[0] = (int)acc;
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc<512>(s_tmem);
+  }
+}
+
 static void appendf(std::string &s, const char *fmt, ...) {
   char buf[512];
   va_list ap;
@@ -295,6 +336,31 @@ int microbench_run(int device, int kind, double *out, int n_out) {
     }
     out[0] = best;
     cudaFree(a); cudaFree(b);
+  } else if (kind == 2) {
+    // TMEM read bandwidth in bytes per SM clock per SM: out[i] for (warps, loads in flight) in
+    // {(4,1),(4,2),(4,4),(8,1),(8,2),(8,4),(16,1),(16,2)}
+    if (major != 10) {
+      set_error("ita_microbench: kind 2 needs an sm_100 device");
+      return ITA_ERR_UNSUPPORTED;
+    }
+    long long *cyc = nullptr;
+    int *sink = nullptr;
+    ITA_CUDA_TRY(cudaMalloc(&cyc, sizeof(long long) * sms));
+    ITA_CUDA_TRY(cudaMalloc(&sink, sizeof(int)));
+    const int cfg[8][2] = {{4, 1}, {4, 2}, {4, 4}, {8, 1}, {8, 2}, {8, 4}, {16, 1}, {16, 2}};
+    const int iters = 4000;
+    for (int i = 0; i < 8 && i < n_out; ++i) {
+      for (int rep = 0; rep < 2; ++rep) {
+        k_tmem_read<<<sms, 512>>>(iters, cfg[i][0], cfg[i][1], cyc, sink);
+        count_launch();
+      }
+      ITA_CUDA_TRY(cudaDeviceSynchronize());
+      long long c0 = 0;
+      ITA_CUDA_TRY(cudaMemcpy(&c0, cyc, sizeof(long long), cudaMemcpyDeviceToHost));
+      out[i] = (double)iters * cfg[i][0] * cfg[i][1] * 4096.0 / (double)c0;
+    }
+    cudaFree(cyc);
+    cudaFree(sink);
   } else {
     set_error("ita_microbench: unknown kind %d", kind);
     return ITA_ERR_INVALID;

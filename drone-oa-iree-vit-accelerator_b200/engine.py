@@ -222,6 +222,6 @@ def selftest(device: int = 0) -> str:
 
 
 def microbench(kind: int, device: int = 0):
-    out = (C.c_double * 4)()
-    L.check(L.load().ita_microbench(device, kind, out, 4), "ita_microbench")
+    out = (C.c_double * 8)()
+    L.check(L.load().ita_microbench(device, kind, out, 8), "ita_microbench")
     return list(out)
