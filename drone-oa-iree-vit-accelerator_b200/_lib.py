@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libita_b200.so")
+LIB_PATH = os.environ.get("ITA_B200_LIB") or os.path.join(_HERE, "libita_b200.so")   # override: developer builds (tracing)
 
 ABI_VERSION = 1
 # enums of include/ita_b200.h

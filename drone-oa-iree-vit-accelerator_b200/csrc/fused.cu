@@ -1,6 +1,7 @@
 // fused.cu -- host side of the fused attention kernel (fused_kernel.cuh): parameter packing (weight panels with the
 // bias-digit K columns, per-stage uniform requant constants), shape/parameter eligibility, launch.
 #include <cuda.h>
+#include <math.h>
 #include <stdlib.h>
 
 #include <vector>
@@ -142,6 +143,42 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
       if (bound[i] >= (1LL << 30)) return no("bias magnitude too large for the fused kernel's s32 accumulate");
   }
 
+  // ---- RQM_FP (requantisation on the FMA pipe, fused_kernel.cuh): per stage an accumulator preset INIT with
+  //      INIT*mult == rnd (mod 2^shift), 0 < INIT - |acc|max, INIT + |acc|max < 2^24, and C = (rnd - INIT*mult)/2^shift + add + 128
+  //      with C < 0 and 256 - C < 2^24 (the ITAmax distance constant m + 128 - C must stay in the linear f32 range).
+  FRq fp[6] = {};
+  bool fp_ok = (mode == RQM_INT_HI);
+  if (const char *e = getenv("ITA_FUSED_FP")) fp_ok = fp_ok && atoi(e) != 0;    // tuning knob: 0 = keep the integer forms
+  for (int i = 0; i < 6 && fp_ok; ++i) {
+    const Rq &r = h->rq_host[stages[i] * h->H];
+    if (r.mult <= 0 || r.shift < 1 || r.shift > 30) { fp_ok = false; break; }
+    int t = 0;
+    while (((r.mult >> t) & 1) == 0) ++t;
+    const int mb = r.shift - t;                                  // INIT is determined modulo 2^mb
+    const long long rnd = r.rnd;
+    if (mb < 0 || (rnd & ((1LL << t) - 1))) { fp_ok = false; break; }
+    long long init;
+    if (mb == 0) {
+      init = 1LL << 23;
+    } else {
+      const long long mo = r.mult >> t, mask = (1LL << mb) - 1;
+      unsigned long long inv = 1;
+      for (int k = 0; k < 6; ++k) inv = inv * (2ULL - (unsigned long long)mo * inv);   // Newton: inverse of the odd part modulo 2^64
+      const long long k0 = (long long)((((unsigned long long)(rnd >> t) & mask) * (inv & mask)) & mask);
+      const long long below = (1LL << 23) - (((1LL << 23) - k0) & mask), above = below + mask + 1;
+      init = ((1LL << 23) - below <= above - (1LL << 23)) ? below : above;
+    }
+    if ((init * r.mult - rnd) & ((1LL << r.shift) - 1)) { fp_ok = false; break; }
+    const long long Cc = (rnd - init * r.mult) / (1LL << r.shift) + r.add + 128;
+    if (init - bound[i] <= 0 || init + bound[i] >= (1LL << 24) || Cc >= 0 || 256 - Cc >= (1LL << 24)) { fp_ok = false; break; }
+    fp[i].init = (int32_t)init;
+    fp[i].negc = (int32_t)-Cc;
+    fp[i].fb = ldexpf((float)r.mult, -r.shift);
+    fp[i].fc = ldexpf((float)Cc, -149);
+    if ((long long)ldexpf(fp[i].fc, 149) != Cc) fp_ok = false;
+  }
+  if (fp_ok) mode = RQM_FP;
+
   FusedPlan *pl = new FusedPlan();
   pl->E = E; pl->P = P; pl->mode = mode; pl->softmax = h->softmax_mode; pl->smem_bytes = shape->smem_bytes;
   const int WA = P * (E + kBiasK), WO = E * (P + kBiasK);
@@ -176,6 +213,8 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     FRq f{};
     if (mode == RQM_TORCH) {
       f.add = r.add; f.eff = r.eff;
+    } else if (mode == RQM_FP) {
+      f = fp[i];
     } else if (mode == RQM_INT_HI) {
       f.multp = (int32_t)((long long)r.mult << (32 - r.shift));
       f.shift = r.shift; f.add = r.add;
@@ -275,13 +314,11 @@ int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, cons
   KernelFn fn = dump ? pl->fn_dump : pl->fn;
 #ifdef ITA_TRACE
   static long long *trace_dev = nullptr;
-  const size_t trace_n = (size_t)(kThreads / 32) * 8 * 32 * 4;
+  const size_t trace_n = (size_t)(kThreads / 32) * (kTraceIters + 1) * 32 * 4;
   const char *trace_file = getenv("ITA_TRACE_FILE");
-  if (trace_file) {
-    if (!trace_dev) cudaMalloc(&trace_dev, trace_n * sizeof(long long));
-    cudaMemsetAsync(trace_dev, 0, trace_n * sizeof(long long), s);
-    prm.trace = trace_dev;
-  }
+  if (!trace_dev) cudaMalloc(&trace_dev, trace_n * sizeof(long long));
+  if (trace_file) cudaMemsetAsync(trace_dev, 0, trace_n * sizeof(long long), s);
+  prm.trace = trace_dev;
 #endif
   fn<<<(unsigned)ctas, kThreads, pl->smem_bytes, s>>>(map, prm);
   count_launch();

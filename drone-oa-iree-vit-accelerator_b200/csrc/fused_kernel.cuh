@@ -60,7 +60,7 @@ constexpr int kBiasK = 32;              // extra K columns carrying the bias dig
 constexpr int kBiasRadix = 127;
 constexpr int kOnesBytes = kS * kBiasK;
 
-enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2 };
+enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2, RQM_FP = 3 };
 enum { STG_Q = 0, STG_K, STG_V, STG_S, STG_AV, STG_O };
 // per-slot mbarriers
 enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2, BAR_EMPTY = 6, BAR_DEP = 10 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */ };
@@ -74,6 +74,11 @@ struct FRq {
   long long c;        // INT_HI: (rnd << (32-shift)) + (add << 32);  INT_GEN: rnd
   int32_t mult32;     // 32-bit form of INT_HI:  (acc * mult32 + c32) >> shift   (host-checked not to overflow)
   int32_t c32;        //   rnd + (add << shift)
+  // FP form (see "requantisation on the FMA pipe" below)
+  int32_t init;       // value the accumulator region is preset to before the stage's first MMA
+  int32_t negc;       // -C
+  float fb;           // mult * 2^-shift
+  float fc;           // C * 2^-149
 };
 
 struct FusedParams {
@@ -153,6 +158,20 @@ struct Cfg {
   }
 };
 
+// ------------------------------------------------------------------------------- requantisation on the FMA pipe (RQM_FP)
+// The integer forms below cost the two scarce pipes (IMAD.HI: 4 fmaheavy cycles per warp; IMAD + SHF: fmaheavy + alu).
+// RQM_FP moves the multiply, the rounding and the shift of  y = ((acc*mult + rnd) >> shift) + add  into ONE FFMA.RM:
+//   * the epilogue that drains an accumulator region presets it (tcgen05.st) to INIT for its next user, and every MMA
+//     accumulates, so TMEM holds bits = INIT + acc with 0 < bits < 2^24.  Read as an f32 such a pattern (exponent field 0
+//     or 1) is exactly bits * 2^-149;
+//   * INIT is chosen per stage with INIT*mult == rnd (mod 2^shift), so C = (rnd - INIT*mult)/2^shift + add + 128 is an
+//     integer and  fma.rm(bits_f32, mult*2^-shift, C*2^-149)  has the exact value ((acc*mult + rnd)/2^shift + add + 128) * 2^-149;
+//     rounding toward -inf at the denormal ulp is the floor, so the result's BIT PATTERN is y + 128 when that is >= 0 and
+//     has the sign bit set when it is negative;
+//   * cvt.pack.sat.u8.s32 of the bit patterns clamps to [0, 255] = sat_s8(y) + 128, and one XOR 0x80808080 per four
+//     elements turns that into s8.  (Checked exhaustively over +-4.3M accumulators x 59 parameter sets on B200:
+//     tools/fp_requant_check.cu.)
+// The ITAmax distance m - a = ceil((m + 128 - C) - bits*mult*2^-shift) is one FFMA.RP the same way.
 // ---------------------------------------------------------------------------------------------------- requant forms
 // ALT selects how INT_HI elements are computed: 0 = one IMAD.HI each; 1 = 32-bit IMAD + SHF each; 2 = alternate (even
 // elements IMAD.HI, odd elements 32-bit) to balance the fma pipe (IMAD.HI occupies it twice as long) against issue slots.
@@ -187,6 +206,8 @@ __device__ __forceinline__ uint32_t pack_u8x4(int y0, int y1, int y2, int y3) {
   asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(y1), "r"(y0), "r"(t));
   return d;
 }
+// RQM_FP: bit pattern of  y + 128  (sign bit set when negative) from the accumulator bit pattern
+__device__ __forceinline__ int rq_fp_bits(uint32_t v, const FRq &r) { return __float_as_int(__fmaf_rd(__uint_as_float(v), r.fb, r.fc)); }
 // X tile [kS rows x E bytes] -> panel layout: one 2-D TMA box (16 B x kS rows) per 16-byte column chunk
 template <int E>
 __device__ __forceinline__ void load_x_tile(void *dst, const CUtensorMap *map, long long frame, uint64_t *bar) {
@@ -202,11 +223,11 @@ __device__ __forceinline__ uint32_t shr_clamp(uint32_t v, uint32_t s) {   // PTX
 }
 
 #ifdef ITA_TRACE
-#define ITA_TR(prm, warp, it, c, k)                                                                             \
-  do {                                                                                                          \
-    if ((prm).trace && blockIdx.x == 0 && (it) < 8 && (threadIdx.x & 31) == 0)                                   \
-      (prm).trace[((((long long)(warp)) * 8 + (it)) * 32 + (c)) * 4 + (k)] = clock64();                          \
-  } while (0)
+// Developer builds: [warp][iteration < 8, 8 = sink][chunk][4] SM clock stamps of CTA 0.  Branch-free (every lane stores to
+// the same word; launches that are not traced still get a buffer), so a stamp is CS2R + STG.
+constexpr int kTraceIters = 8;
+#define ITA_TR(prm, warp, it, c, k)                                                                                          \
+  (prm).trace[((((long long)(warp)) * (kTraceIters + 1) + ((blockIdx.x == 0 && (it) < kTraceIters) ? (it) : kTraceIters)) * 32 + (c)) * 4 + (k)] = clock64()
 #else
 #define ITA_TR(prm, warp, it, c, k) do { } while (0)
 #endif
@@ -245,7 +266,22 @@ __device__ __forceinline__ void tmem_pin32(uint32_t (&v)[32]) {
 
 // Walk NG groups of 32 accumulator columns of this thread's row, software-pipelined: the TMEM load of group g+1 is in
 // flight while f(g, v) works on group g.  addr(g) gives the TMEM address of group g.  After the last load has landed,
-// `done()` runs once (used to hand the TMEM region back to the MMA thread).
+// `done.issue()` runs once, and `done.finish()` after the last group has been processed (together they hand the TMEM
+// region back to the MMA thread; the split lets the RQM_FP preset stores overlap the last group's arithmetic).
+struct NoRelease {
+  __device__ __forceinline__ void issue() const {}
+  __device__ __forceinline__ void finish() const {}
+};
+template <class I, class Fn>
+struct Release {
+  I issue_fn;
+  Fn finish_fn;
+  __device__ __forceinline__ void issue() { issue_fn(); }
+  __device__ __forceinline__ void finish() { finish_fn(); }
+};
+template <class I, class Fn>
+__device__ __forceinline__ Release<I, Fn> make_release(I i, Fn f) { return Release<I, Fn>{i, f}; }
+
 template <int NG, class A, class F, class D>
 __device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
   uint32_t va[32], vb[32];
@@ -259,9 +295,10 @@ __device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
       tmem_ld32(addr(g + 1), nxt);
       tmem_pin32(cur);              // keeps the compiler from hoisting the work on `cur` above the load just issued
     }
-    if constexpr (g + 1 == NG) done();
+    if constexpr (g + 1 == NG) done.issue();
     f(gg, cur);
     if constexpr (g + 1 < NG) tmem_wait32(nxt);
+    if constexpr (g + 1 == NG) done.finish();
   });
 }
 
@@ -277,9 +314,15 @@ __device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const F
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       int y[4];
+      if constexpr (MODE == RQM_FP) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) y[i] = rq_apply<MODE, ALT>((int)v[j + q * 4 + i], r, i);
-      w[q] = pack_s8x4(y[0], y[1], y[2], y[3]);
+        for (int i = 0; i < 4; ++i) y[i] = rq_fp_bits(v[j + q * 4 + i], r);
+        w[q] = pack_u8x4(y[0], y[1], y[2], y[3]) ^ 0x80808080u;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) y[i] = rq_apply<MODE, ALT>((int)v[j + q * 4 + i], r, i);
+        w[q] = pack_s8x4(y[0], y[1], y[2], y[3]);
+      }
     }
     const uint4 o = make_uint4(w[0], w[1], w[2], w[3]);
     if (panel) *reinterpret_cast<uint4 *>(panel + ((col + j) >> 4) * (kS * 16) + row * 16) = o;
@@ -326,7 +369,7 @@ __device__ __forceinline__ void itamax_repo_half(uint32_t t, const FRq &rq, int8
 #pragma unroll
                  for (int i = 0; i < 32; ++i) amax = max(amax, (int)v[i]);
                },
-               [] {});
+               NoRelease{});
   mine->x = amax;
   pair_sync(pc);
   amax = max(amax, other->x);
@@ -349,7 +392,7 @@ __device__ __forceinline__ void itamax_repo_half(uint32_t t, const FRq &rq, int8
 #pragma unroll
                    for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist((int)v[i], i));
                  },
-                 [] {});
+                 NoRelease{});
     mine->y = (int)sum;
     pair_sync(pc);
     sum += (uint32_t)other->y;
@@ -382,7 +425,7 @@ __device__ __forceinline__ void itamax_repo_half(uint32_t t, const FRq &rq, int8
 #pragma unroll
                    for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist((int)v[i]));
                  },
-                 [] {});
+                 NoRelease{});
     mine->y = (int)sum;
     pair_sync(pc);
     sum += (uint32_t)other->y;
@@ -419,7 +462,109 @@ __device__ __forceinline__ void itamax_repo_half(uint32_t t, const FRq &rq, int8
   //  reaches after its read of the old value)
 }
 
-// Recalled golden-model streaming softmax (oracle/ita_ref.py itamax_stream16): 16-column groups in
+// The same ITAmax with the requantisation on the FMA pipe (RQM_FP).  TMEM holds bits = INIT + acc (monotone in acc), so
+// pass 1 takes the max of the raw patterns; z = rq_fp_bits(.) is a + 128 before saturation.  Fast rows (no logit
+// saturates high, m >= -119) get the distance d = m - a from one FFMA.RP per element; other rows clamp explicitly.
+template <bool DUMP, int HALF, class R>
+__device__ __forceinline__ void itamax_repo_half_fp(uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
+                                                    const PairCtx &pc, R &&release) {
+  auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
+  int2 *mine = pc.xch + HALF * kS + row, *other = pc.xch + (HALF ^ 1) * kS + row;
+  int amax = 0;                                   // patterns are positive
+  tmem_walk<2>(addr,
+               [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                 for (int i = 0; i < 32; ++i) amax = max(amax, (int)v[i]);
+               },
+               NoRelease{});
+  mine->x = amax;
+  pair_sync(pc);
+  amax = max(amax, other->x);
+  const int zmax = rq_fp_bits((uint32_t)amax, rq);
+  const int mp = min(max(zmax, 0), 255);          // m + 128
+  bool fast = false;
+#ifndef ITA_FP_NOFAST
+  if constexpr (!DUMP) fast = __all_sync(0xffffffffu, zmax <= 255 && zmax >= 9);
+#endif
+  uint32_t sum = 0;
+  auto store16 = [&](int g, int j, const uint4 &ov) {
+    *reinterpret_cast<uint4 *>(k_buf + ((HALF * 64 + g * 32 + j) >> 4) * (kS * 16) + row * 16) = ov;
+  };
+  if (fast) {
+    // d + 1 = ceil((m + 129 - C) - bits*b) is >= 1 for every element of the row (an exact value in (-1, 0) would round to
+    // -0.0, whose pattern is not 0), so the shifts below work on 2*256 and 2*inv8
+    const float c2 = __int_as_float(mp + 1 + rq.negc), nfb = -rq.fb;
+    auto dist = [&](uint32_t v) -> uint32_t { return (uint32_t)__float_as_int(__fmaf_ru(__uint_as_float(v), nfb, c2)); };
+    tmem_walk<2>(addr,
+                 [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                   for (int i = 0; i < 32; ++i) sum += shr_clamp(512u, dist(v[i]));
+                 },
+                 NoRelease{});
+    mine->y = (int)sum;
+    pair_sync(pc);
+    sum += (uint32_t)other->y;
+    const uint32_t inv8 = (((255u * 65536u) / sum) >> 8) << 1;
+    tmem_walk<2>(addr,
+                 [&](auto gg, const uint32_t(&v)[32]) {
+                   constexpr int g = decltype(gg)::value;
+#pragma unroll
+                   for (int j = 0; j < 32; j += 16) {
+                     uint32_t w[4];
+#pragma unroll
+                     for (int q = 0; q < 4; ++q) {
+                       int o[4];
+#pragma unroll
+                       for (int i = 0; i < 4; ++i) o[i] = (int)shr_clamp(inv8, dist(v[j + q * 4 + i]));
+                       w[q] = pack_u8x4(o[0], o[1], o[2], o[3]);
+                     }
+                     store16(g, j, make_uint4(w[0], w[1], w[2], w[3]));
+                   }
+                 },
+                 release);
+  } else {
+    auto dist = [&](uint32_t v) -> uint32_t { return (uint32_t)(mp - min(max(rq_fp_bits(v, rq), 0), 255)); };
+    tmem_walk<2>(addr,
+                 [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                   for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist(v[i]));
+                 },
+                 NoRelease{});
+    mine->y = (int)sum;
+    pair_sync(pc);
+    sum += (uint32_t)other->y;
+    const uint32_t inv8 = ((255u * 65536u) / sum) >> 8;
+    tmem_walk<2>(addr,
+                 [&](auto gg, const uint32_t(&v)[32]) {
+                   constexpr int g = decltype(gg)::value;
+#pragma unroll
+                   for (int j = 0; j < 32; j += 16) {
+                     uint32_t w[4], wa[4];
+#pragma unroll
+                     for (int q = 0; q < 4; ++q) {
+                       int o[4], a[4];
+#pragma unroll
+                       for (int i = 0; i < 4; ++i) {
+                         const uint32_t d = dist(v[j + q * 4 + i]);
+                         o[i] = (int)shr_clamp(inv8, d);
+                         a[i] = mp - 128 - (int)d;
+                       }
+                       w[q] = pack_u8x4(o[0], o[1], o[2], o[3]);
+                       if constexpr (DUMP) wa[q] = pack_s8x4(a[0], a[1], a[2], a[3]);
+                     }
+                     const uint4 ov = make_uint4(w[0], w[1], w[2], w[3]);
+                     store16(g, j, ov);
+                     if constexpr (DUMP) {
+                       if (gAsm) *reinterpret_cast<uint4 *>(gAsm + HALF * 64 + g * 32 + j) = ov;
+                       if (gA) *reinterpret_cast<uint4 *>(gA + HALF * 64 + g * 32 + j) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
+                     }
+                   }
+                 },
+                 release);
+  }
+}
+
+// Recalled golden-model streaming softmax (the stream16 variant): 16-column groups in
 // column order, running max m and denominator, eps = 1/32 with round-half-up; then out = inv >> rhu((m - a) / 32).
 // The row is walked in column order: HALF 1 continues from the state HALF 0 publishes.
 template <int MODE, bool DUMP, int HALF, class R>
@@ -427,7 +572,11 @@ __device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, in
                                                    const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
   auto biased = [&](uint32_t acc) -> uint32_t {   // sat8(requant) + 128 in [0, 255]
-    return (uint32_t)(min(max(rq_apply<MODE, 0>((int)acc, rq, 0), -128), 127) + 128);
+    if constexpr (MODE == RQM_FP) {
+      return (uint32_t)min(max(rq_fp_bits(acc, rq), 0), 255);
+    } else {
+      return (uint32_t)(min(max(rq_apply<MODE, 0>((int)acc, rq, 0), -128), 127) + 128);
+    }
   };
   int2 *st0 = pc.xch + row, *st1 = pc.xch + kS + row;
   uint32_t m = 0, tot = 0;
@@ -455,7 +604,7 @@ __device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, in
                    for (int i = 0; i < 16; ++i) tot += 256u >> ((m - b[i] + 16) >> 5);
                  }
                },
-               [] {});
+               NoRelease{});
   if constexpr (HALF == 0) {
     *st0 = make_int2((int)m, (int)tot);
     pair_sync(pc);
@@ -509,6 +658,20 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
   int8_t *const q_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_Q, *const k_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_K,
                *const v_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_V;
   bool ok = true;
+  if constexpr (MODE == RQM_FP && WG == 0) {
+    // preset the accumulator ring for the first kRegions chunks (phase 0 of the EMPTY barriers)
+    static_for<0, kRegions>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      const uint32_t v = (uint32_t)prm.rq[C::stage_of(r)].init;
+      tmem_fill32(t_lane + r * kRegionCols, v);
+      tmem_fill32(t_lane + r * kRegionCols + 32, v);
+    });
+    tmem_st_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0)
+      for (int r = 0; r < kRegions; ++r) mbar_arrive(sc.bars + BAR_EMPTY + r);
+  }
   for (long long it = 0; it < iters && ok; ++it) {
     const long long f = frame0 + it * frame_stride;
     static_for<0, C::NCH>([&](auto cc) {
@@ -523,12 +686,29 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
         ITA_TR(prm, threadIdx.x >> 5, it, c, 1);
         tc_fence_after();
         const uint32_t taddr = t_lane + r * kRegionCols;
-        auto release = [&] {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(sc.bars + BAR_EMPTY + r);
-          ITA_TR(prm, threadIdx.x >> 5, it, c, 2);
-        };
+        // hand the region back: (RQM_FP: preset it for its next user, chunk c + kRegions, first) then arrive on EMPTY
+        auto release = make_release(
+            [&] {
+              if constexpr (MODE == RQM_FP) {
+                const uint32_t v = (uint32_t)prm.rq[C::stage_of((c + kRegions) % C::NCH)].init;
+                tmem_fill32(taddr, v);
+                tmem_fill32(taddr + 32, v);
+              } else {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sc.bars + BAR_EMPTY + r);
+                ITA_TR(prm, threadIdx.x >> 5, it, c, 2);
+              }
+            },
+            [&] {
+              if constexpr (MODE == RQM_FP) {
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sc.bars + BAR_EMPTY + r);
+                ITA_TR(prm, threadIdx.x >> 5, it, c, 2);
+              }
+            });
         if constexpr (stage == STG_S) {
           // ---- logits: this warpgroup's 64 key columns -> ITAmax -> Asm (u8) into the K buffer
           int8_t *gA = nullptr;
@@ -537,7 +717,9 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
             if (prm.dA) gA = prm.dA + (f * kS + row) * kS;
             if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
           }
-          if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
+          if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && MODE == RQM_FP)
+            itamax_repo_half_fp<DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+          else if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
             itamax_repo_half<MODE, ALT, DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
           else
             itamax_stream_half<MODE, DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
@@ -665,7 +847,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
           if (!ok) return;
           const uint32_t use = (uint32_t)(it * (C::NCH / kRegions)) + c / kRegions;
           ITA_TR(prm, warp, it, c, 0);
-          if constexpr (C::needs_empty_wait(c)) {
+          if constexpr (MODE == RQM_FP) {
+            // EMPTY phase `use` = "region preset for its use-th user" (phase 0: the initial preset)
+            if (C::needs_empty_wait(c) || use == 0) ok = mbar_wait(b + BAR_EMPTY + r, use & 1, prm.abort_flag);
+          } else if constexpr (C::needs_empty_wait(c)) {
             if (use > 0) ok = mbar_wait(b + BAR_EMPTY + r, (use - 1) & 1, prm.abort_flag);
           }
           ITA_TR(prm, warp, it, c, 1);
@@ -679,6 +864,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
           tc_fence_after();
           ITA_TR(prm, warp, it, c, 2);
           const uint32_t d_tmem = d_base + r * kRegionCols;
+          constexpr uint32_t acc0 = MODE == RQM_FP ? 1u : 0u;        // RQM_FP: the region is preset, every MMA accumulates
           if (leader) {
             if constexpr (stage <= STG_V) {
               // projections: A = X [S rows, K = E] K-major; B = rows [64 idx, +64) of W_t^T [P rows, K = E + 32] K-major;
@@ -687,7 +873,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
 #pragma unroll
               for (int k = 0; k < E / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(x16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(w16, wt + k * 2 * P * 16, P * 16, 128), ID_PROJ, k > 0);
+                        make_smem_desc_rel(w16, wt + k * 2 * P * 16, P * 16, 128), ID_PROJ, k > 0 ? 1u : acc0);
               umma_i8(d_tmem, make_smem_desc_rel(ones16, 0, kS * 16, 128), make_smem_desc_rel(w16, wt + (E / 16) * P * 16, P * 16, 128),
                       ID_PROJ, 1);
             } else if constexpr (stage == STG_S) {
@@ -695,20 +881,20 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
 #pragma unroll
               for (int k = 0; k < P / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(k16, idx * 64 * 16 + k * 2 * kS * 16, kS * 16, 128), ID_QK, k > 0);
+                        make_smem_desc_rel(k16, idx * 64 * 16 + k * 2 * kS * 16, kS * 16, 128), ID_QK, k > 0 ? 1u : acc0);
             } else if constexpr (stage == STG_AV) {
               // context: A = Asm [S, K = S] u8 K-major (in the K buffer); B = columns [64 idx, +64) of V [K = S rows, N = P] MN-major
 #pragma unroll
               for (int k = 0; k < kS / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(v16, idx * 4 * kS * 16 + k * 32 * 16, 128, kS * 16), ID_AV, k > 0);
+                        make_smem_desc_rel(v16, idx * 4 * kS * 16 + k * 32 * 16, 128, kS * 16), ID_AV, k > 0 ? 1u : acc0);
             } else {
               // output projection: A = O [S, K = P] K-major (in the Q buffer); B = rows [OC idx, +OC) of Wo^T [E rows, K = P + 32]
               constexpr uint32_t wo = 3 * C::WA_BYTES + idx * C::OC * 16;
 #pragma unroll
               for (int k = 0; k < P / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128), make_smem_desc_rel(w16, wo + k * 2 * E * 16, E * 16, 128),
-                        ID_O, k > 0);
+                        ID_O, k > 0 ? 1u : acc0);
               umma_i8(d_tmem, make_smem_desc_rel(ones16, 0, kS * 16, 128), make_smem_desc_rel(w16, wo + (P / 16) * E * 16, E * 16, 128), ID_O, 1);
             }
             umma_commit(b + BAR_FULL + r);
@@ -773,6 +959,7 @@ struct FusedShape {
   ITA_FUSED_ALT1(E, P, SM)                                                                                            \
   if (mode == RQM_INT_HI && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_HI, SM, 0, true> : k_ita_fused<E, P, RQM_INT_HI, SM, 0, false>;     \
   if (mode == RQM_INT_GEN && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_GEN, SM, 0, true> : k_ita_fused<E, P, RQM_INT_GEN, SM, 0, false>; \
+  if (mode == RQM_FP && softmax == SM) return dump ? k_ita_fused<E, P, RQM_FP, SM, 0, true> : k_ita_fused<E, P, RQM_FP, SM, 0, false>;           \
   if (mode == RQM_TORCH && softmax == SM) return dump ? k_ita_fused<E, P, RQM_TORCH, SM, 0, true> : k_ita_fused<E, P, RQM_TORCH, SM, 0, false>;
 
 #define ITA_FUSED_DEFINE_SHAPE(E, P)                                              \

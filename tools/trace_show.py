@@ -1,13 +1,14 @@
 """Developer tool: print the per-chunk timeline recorded by tools/trace_run.py (cycles relative to the iteration start)."""
 import sys
 import numpy as np
-t = np.fromfile(sys.argv[1], dtype=np.int64).reshape(19, 8, 32, 4)
+t = np.fromfile(sys.argv[1], dtype=np.int64).reshape(19, 9, 32, 4)
 NQ = 3
 names = ["Q0", "Q1", "Q2", "V0", "V1", "V2", "K0", "K1", "K2", "S0", "S1", "AV0", "AV1", "AV2", "O0", "O1"]
 it = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 for slot in (0, 1):
     mma = 16 + slot
     base = t[mma, it, 0, 0]
+    print(f"==== slot {slot}: base - slot0 base = {base - t[16, it, 0, 0]}")
     print(f"==== slot {slot} iteration {it}: frame period (MMA Q0 start -> next Q0 start) = {t[mma, it + 1, 0, 0] - base} cycles")
     print("chunk  | MMA: wait0  gotEmpty  gotDeps  committed | EPI(warp q0 of owner): wait0 full released done | dur")
     for c, nm in enumerate(names):
