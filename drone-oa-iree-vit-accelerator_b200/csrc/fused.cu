@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "fused_kernel.cuh"
@@ -82,6 +83,24 @@ static bool bias_digits(int32_t b, int8_t *g) {
   return q == 0;
 }
 
+// non-negative value -> n unsigned digits g with  v = g[0] + kBiasRadixU * (g[1] + ... + g[n-1]),  every g in [0, 255]
+static bool offset_digits(long long v, int n, int8_t *g) {
+  if (v < 0) return false;
+  long long q = v / kBiasRadixU;
+  g[0] = (int8_t)(uint8_t)(v % kBiasRadixU);
+  for (int j = 1; j < n; ++j) {
+    long long t = q > 255 ? 255 : q;
+    g[j] = (int8_t)(uint8_t)t;
+    q -= t;
+  }
+  return q == 0;
+}
+// 8-row constant tile [8 x ncols] whose rows are all `row`, in the panel layout ([ncols/16][8][16])
+static void const_tile(int8_t *dst, int ncols, const int8_t *row) {
+  for (int c = 0; c < ncols; ++c)
+    for (int r = 0; r < 8; ++r) dst[(size_t)(c / 16) * 128 + r * 16 + (c % 16)] = row[c];
+}
+
 int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   h->fused = nullptr;
   auto no = [&](const std::string &why) {
@@ -143,12 +162,15 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
       if (bound[i] >= (1LL << 30)) return no("bias magnitude too large for the fused kernel's s32 accumulate");
   }
 
-  // ---- RQM_FP (requantisation on the FMA pipe, fused_kernel.cuh): per stage an accumulator preset INIT with
-  //      INIT*mult == rnd (mod 2^shift), 0 < INIT - |acc|max, INIT + |acc|max < 2^24, and C = (rnd - INIT*mult)/2^shift + add + 128
-  //      with C < 0 and 256 - C < 2^24 (the ITAmax distance constant m + 128 - C must stay in the linear f32 range).
+  // ---- RQM_FP (requantisation on the FMA pipe, fused_kernel.cuh): per stage an accumulator offset INIT with
+  //      INIT*mult == rnd (mod 2^shift), INIT > |acc|max, INIT + |acc|max < 2^24, and C = (rnd - INIT*mult)/2^shift + add + 128
+  //      with C < 0 and 257 - C < 2^24 (the ITAmax distance constant m + 129 - C must stay in the linear f32 range); the offset
+  //      (plus the bias) must fit the unsigned digits of the stage's digit K steps.
   FRq fp[6] = {};
   bool fp_ok = (mode == RQM_INT_HI);
   if (const char *e = getenv("ITA_FUSED_FP")) fp_ok = fp_ok && atoi(e) != 0;    // tuning knob: 0 = keep the integer forms
+  const long long cap32 = kBiasRadixU - 1 + (long long)kBiasRadixU * 255 * (kBiasK - 1);
+  const long long cap64 = kBiasRadixU - 1 + (long long)kBiasRadixU * 255 * (kBiasKO - 1);
   for (int i = 0; i < 6 && fp_ok; ++i) {
     const Rq &r = h->rq_host[stages[i] * h->H];
     if (r.mult <= 0 || r.shift < 1 || r.shift > 30) { fp_ok = false; break; }
@@ -157,20 +179,23 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     const int mb = r.shift - t;                                  // INIT is determined modulo 2^mb
     const long long rnd = r.rnd;
     if (mb < 0 || (rnd & ((1LL << t) - 1))) { fp_ok = false; break; }
-    long long init;
-    if (mb == 0) {
-      init = 1LL << 23;
-    } else {
+    // |acc|max; for A.V with the repo ITAmax the probabilities of a row sum to <= 255 (sum_k (n_k*inv >> 16) <= 255*sum n/sum n)
+    const long long bnd = (i == 4 && h->softmax_mode == ITA_SOFTMAX_REPO_GLOBAL) ? 255LL * 128 : bound[i];
+    const long long lo = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
+    long long init = lo;
+    if (mb > 0) {
       const long long mo = r.mult >> t, mask = (1LL << mb) - 1;
       unsigned long long inv = 1;
       for (int k = 0; k < 6; ++k) inv = inv * (2ULL - (unsigned long long)mo * inv);   // Newton: inverse of the odd part modulo 2^64
       const long long k0 = (long long)((((unsigned long long)(rnd >> t) & mask) * (inv & mask)) & mask);
-      const long long below = (1LL << 23) - (((1LL << 23) - k0) & mask), above = below + mask + 1;
-      init = ((1LL << 23) - below <= above - (1LL << 23)) ? below : above;
+      init = lo + ((k0 - lo) & mask);                            // smallest value >= lo congruent to k0
     }
     if ((init * r.mult - rnd) & ((1LL << r.shift) - 1)) { fp_ok = false; break; }
     const long long Cc = (rnd - init * r.mult) / (1LL << r.shift) + r.add + 128;
-    if (init - bound[i] <= 0 || init + bound[i] >= (1LL << 24) || Cc >= 0 || 256 - Cc >= (1LL << 24)) { fp_ok = false; break; }
+    // the stage's digit capacity: bias + offset (projections: one step; output projection, logits: two; context: one)
+    const long long bmx = (i < 3) ? bound[i] - (long long)E * 128 * 128 : (i == 5 ? bound[i] - (long long)P * 128 * 128 : 0);
+    const long long cap = (i == 3 || i == 5) ? cap64 : cap32;
+    if (init + bnd >= (1LL << 24) || init + bmx > cap || Cc >= 0 || 257 - Cc >= (1LL << 24)) { fp_ok = false; break; }
     fp[i].init = (int32_t)init;
     fp[i].negc = (int32_t)-Cc;
     fp[i].fb = ldexpf((float)r.mult, -r.shift);
@@ -181,25 +206,49 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
 
   FusedPlan *pl = new FusedPlan();
   pl->E = E; pl->P = P; pl->mode = mode; pl->softmax = h->softmax_mode; pl->smem_bytes = shape->smem_bytes;
-  const int WA = P * (E + kBiasK), WO = E * (P + kBiasK);
-  const size_t wbytes = (size_t)3 * WA + WO + kOnesBytes;
-  std::vector<int8_t> host(wbytes);
-  // W_t^T as [N = P rows, K = E + 32 cols]: element (n, k) = W[k][n] (golden layout W [E,P]); then the bias digits of column n
-  const int8_t *Ws[3] = {d->Wq, d->Wk, d->Wv};
-  const int32_t *Bs[3] = {d->Bq, d->Bk, d->Bv};
+  const int WA = P * (E + kBiasK), WO = E * (P + kBiasKO);
+  const size_t wbytes = (size_t)3 * WA + WO + kConstBytes;
+  std::vector<int8_t> host(wbytes, 0);
+  const bool fpm = (mode == RQM_FP);
+  // stage index (Q K V QK AV O) of the three concatenated projections Q | V | K
+  const int cat_stage[3] = {0, 2, 1};
+  // [Wq | Wv | Wk]^T as ONE matrix [N = 3P rows, K = E + 32 cols] (the kernel's projection chunks are 128 consecutive rows of
+  // it): row n = t*P + j holds column j of W_t (golden layout W [E,P]), then the digits of that column's bias (RQM_FP:
+  // bias + the stage's offset, unsigned)
+  const int8_t *Ws[3] = {d->Wq, d->Wv, d->Wk};
+  const int32_t *Bs[3] = {d->Bq, d->Bv, d->Bk};
   bool digits_ok = true;
-  std::vector<int8_t> dig((size_t)(P > E ? P : E) * kBiasK);
-  for (int t = 0; t < 3; ++t) {
-    for (int n = 0; n < P; ++n) digits_ok = bias_digits(Bs[t][n], &dig[(size_t)n * kBiasK]) && digits_ok;
-    to_panels(host.data() + (size_t)t * WA, P, E + kBiasK,
-              [&](int n, int k) { return k < E ? Ws[t][(size_t)k * P + n] : dig[(size_t)n * kBiasK + (k - E)]; });
+  std::vector<int8_t> dig((size_t)(3 * P > E ? 3 * P : E) * kBiasKO, 0);
+  for (int t = 0; t < 3; ++t)
+    for (int n = 0; n < P; ++n) {
+      int8_t *g = &dig[(size_t)(t * P + n) * kBiasK];
+      digits_ok = (fpm ? offset_digits((long long)Bs[t][n] + fp[cat_stage[t]].init, kBiasK, g) : bias_digits(Bs[t][n], g)) && digits_ok;
+    }
+  to_panels(host.data(), 3 * P, E + kBiasK, [&](int n, int k) {
+    return k < E ? Ws[n / P][(size_t)k * P + (n % P)] : dig[(size_t)n * kBiasK + (k - E)];
+  });
+  // Wo^T as [N = E rows, K = P + 64 cols]: element (n, k) = Wo[k][n]  (golden layout Wo [P,E]); 64 digit columns (the integer
+  // forms use the first 32)
+  std::fill(dig.begin(), dig.end(), 0);
+  for (int n = 0; n < E; ++n) {
+    int8_t *g = &dig[(size_t)n * kBiasKO];
+    digits_ok = (fpm ? offset_digits((long long)d->Bo[n] + fp[5].init, kBiasKO, g) : bias_digits(d->Bo[n], g)) && digits_ok;
   }
-  // Wo^T as [N = E rows, K = P + 32 cols]: element (n, k) = Wo[k][n]  (golden layout Wo [P,E])
-  for (int n = 0; n < E; ++n) digits_ok = bias_digits(d->Bo[n], &dig[(size_t)n * kBiasK]) && digits_ok;
-  to_panels(host.data() + (size_t)3 * WA, E, P + kBiasK,
-            [&](int n, int k) { return k < P ? d->Wo[(size_t)k * E + n] : dig[(size_t)n * kBiasK + (k - P)]; });
-  // constant A tile of the bias K step: every row is [1, 127, ..., 127]
-  to_panels(host.data() + (size_t)3 * WA + WO, kS, kBiasK, [&](int, int k) { return (int8_t)(k == 0 ? 1 : kBiasRadix); });
+  to_panels(host.data() + (size_t)3 * WA, E, P + kBiasKO,
+            [&](int n, int k) { return k < P ? d->Wo[(size_t)k * E + n] : dig[(size_t)n * kBiasKO + (k - P)]; });
+  // constant tiles: A operand of the digit steps [1, R, ..., R]; RQM_FP: the offset digits of Q.K^T and A.V
+  {
+    int8_t row[64];
+    for (int k = 0; k < 64; ++k) row[k] = (int8_t)(uint8_t)(k == 0 ? 1 : (fpm ? kBiasRadixU : kBiasRadix));
+    int8_t *ca = host.data() + (size_t)3 * WA + WO;
+    const_tile(ca, 64, row);
+    if (fpm) {
+      digits_ok = offset_digits(fp[3].init, 64, row) && digits_ok;
+      const_tile(ca + kConstABytes, 64, row);
+      digits_ok = offset_digits(fp[4].init, 32, row) && digits_ok;
+      const_tile(ca + kConstABytes + kConstQKBytes, 32, row);
+    }
+  }
   if (!digits_ok) {
     delete pl;
     return no("a bias exceeds the range the fused kernel folds into the MMA (|b| <= 127*31*127)");

@@ -52,18 +52,25 @@ constexpr int kEpiWarpsPerSlot = 8;
 constexpr int kWarpMma = kSlots * kEpiWarpsPerSlot;     // + slot
 constexpr int kWarpLoad = kWarpMma + kSlots;
 constexpr int kThreads = (kWarpLoad + 1) * 32;
-constexpr int kRegions = 4;             // accumulator ring per slot
-constexpr int kRegionCols = 64;
+constexpr int kRegions = 2;             // accumulator ring per slot
+constexpr int kRegionCols = 128;
 constexpr int kTmemColsPerSlot = kRegions * kRegionCols;
 constexpr int kBarsPerSlot = 16;
-constexpr int kBiasK = 32;              // extra K columns carrying the bias digits
-constexpr int kBiasRadix = 127;
-constexpr int kOnesBytes = kS * kBiasK;
+constexpr int kBiasK = 32;              // extra K columns carrying the bias digits (one K step)
+constexpr int kBiasKO = 64;             // the output projection reserves two such steps (RQM_FP needs the range)
+constexpr int kBiasRadix = 127;         // signed digits (integer requant forms)
+constexpr int kBiasRadixU = 255;        // unsigned digits (RQM_FP)
+// Constant operand tiles, 8 rows each, read with SBO = 0 so that every 8-row group of the MMA operand aliases them:
+//   CA  [8 x 64]  A operand of the digit K steps: rows [1, R, R, ..., R]  (R = 127 s8 / 255 u8)
+//   DQK [8 x 64]  B operand of the two offset steps of Q.K^T (RQM_FP)     DAV [8 x 32]  B operand of the offset step of A.V
+constexpr int kConstABytes = 8 * 64, kConstQKBytes = 8 * 64, kConstAVBytes = 8 * 32;
+constexpr int kConstBytes = kConstABytes + kConstQKBytes + kConstAVBytes;
 
 enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2, RQM_FP = 3 };
 enum { STG_Q = 0, STG_K, STG_V, STG_S, STG_AV, STG_O };
 // per-slot mbarriers
-enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2, BAR_EMPTY = 6, BAR_DEP = 10 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */ };
+enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2 /* + region */, BAR_EMPTY = 4 /* + region */, BAR_DEP = 6 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */ };
+enum { CK_PROJ = 0, CK_S, CK_AV, CK_O };   // chunk kinds
 
 // Per-stage uniform requant parameters as the fused kernel consumes them.
 struct FRq {
@@ -75,7 +82,7 @@ struct FRq {
   int32_t mult32;     // 32-bit form of INT_HI:  (acc * mult32 + c32) >> shift   (host-checked not to overflow)
   int32_t c32;        //   rnd + (add << shift)
   // FP form (see "requantisation on the FMA pipe" below)
-  int32_t init;       // value the accumulator region is preset to before the stage's first MMA
+  int32_t init;       // offset the digit K steps add to every accumulator of the stage
   int32_t negc;       // -C
   float fb;           // mult * 2^-shift
   float fc;           // C * 2^-149
@@ -97,20 +104,23 @@ struct FusedParams {
 template <int E, int P>
 struct Cfg {
   static constexpr int S = kS;
-  static constexpr int NQ = P / 64;                                      // chunks per projection / per A.V
-  static constexpr int NCH = 4 * NQ + 4;                                 // chunks per frame
-  static constexpr int OC = E / 2;                                       // columns per output-projection chunk
-  static constexpr int WA_BYTES = P * (E + kBiasK);                      // each of Wq^T, Wk^T, Wv^T with bias digits
-  static constexpr int WO_BYTES = E * (P + kBiasK);                      // Wo^T with bias digits
+  static constexpr int PW = 3 * P;                                       // concatenated projection output: Q | V | K
+  static constexpr int NPC = (PW + 127) / 128;                           // projection chunks (128 columns, the last may be 64)
+  static constexpr int NAVC = (P + 127) / 128;                           // A.V chunks
+  static constexpr int NCH = NPC + NAVC + 2;                             // + logits + output projection
+  static constexpr int C_S = NPC, C_AV0 = NPC + 1, C_O = NPC + 1 + NAVC;
+  static constexpr int WP_BYTES = PW * (E + kBiasK);                     // [Wq | Wv | Wk]^T with bias digits
+  static constexpr int WO_BYTES = E * (P + kBiasKO);                     // Wo^T with bias digits
   static constexpr int OFF_W = 0;
-  static constexpr int OFF_ONES = 3 * WA_BYTES + WO_BYTES;
-  static constexpr int WPANEL_BYTES = OFF_ONES + kOnesBytes;             // what is bulk-copied at kernel start
+  static constexpr int OFF_WO = WP_BYTES;
+  static constexpr int OFF_CA = WP_BYTES + WO_BYTES, OFF_DQK = OFF_CA + kConstABytes, OFF_DAV = OFF_DQK + kConstQKBytes;
+  static constexpr int WPANEL_BYTES = OFF_CA + kConstBytes;              // what is bulk-copied at kernel start
   static constexpr int X_BYTES = S * E;
   static constexpr int SP_BYTES = S * P;
   static constexpr int KA_BYTES = (S * P > S * S) ? S * P : S * S;       // K, later the softmax output
   // the next frame's X tile lives in the part of the K buffer that the softmax output does not cover, when it fits and
-  // only the last K chunk overlaps it (that chunk's epilogue runs after the last MMA that reads X)
-  static constexpr bool X_IN_KTAIL = (S * S + X_BYTES <= KA_BYTES) && ((NQ - 1) * 64 * S <= S * S);
+  // only the last projection chunk writes K columns there (that chunk's epilogue runs after the last MMA that reads X)
+  static constexpr bool X_IN_KTAIL = (S * S + X_BYTES <= KA_BYTES) && (2 * P + S >= 128 * (NPC - 1));
   static constexpr int OFF_Q = 0, OFF_K = SP_BYTES, OFF_V = OFF_K + KA_BYTES;
   static constexpr int OFF_X = X_IN_KTAIL ? OFF_K + S * S : OFF_V + SP_BYTES;
   static constexpr int SLOT_BYTES = OFF_V + SP_BYTES + (X_IN_KTAIL ? 0 : X_BYTES);
@@ -119,51 +129,46 @@ struct Cfg {
   static constexpr int XCHG_BYTES = kSlots * 2 * S * 8;
   static constexpr int OFF_BAR = OFF_XCHG + XCHG_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 512;
-  static_assert(E % 32 == 0 && P % 64 == 0, "E must be a multiple of 32 (tcgen05 kind::i8 K) and P of 64 (chunk width)");
-  static_assert(OC % 32 == 0 && OC <= kRegionCols, "output-projection chunks must be 32 or 64 columns");
-  static_assert(NCH % kRegions == 0, "chunks per frame must tile the accumulator ring");
+  static_assert(E % 64 == 0 && E <= 128 && P % 64 == 0, "E in {64, 128} (one output chunk), P a multiple of 64 (sub-block width)");
   static_assert((1 + kSlots * kBarsPerSlot) * 8 + 8 <= 512, "barrier area");
   static_assert(WPANEL_BYTES % 16 == 0 && SLOT_BYTES % 128 == 0, "alignment");
-  // chunk c of a frame -> stage, index within the stage, first column, width
-  static constexpr int stage_of(int c) {
-    return c < NQ ? STG_Q : c < 2 * NQ ? STG_V : c < 3 * NQ ? STG_K : c < 3 * NQ + 2 ? STG_S : c < 4 * NQ + 2 ? STG_AV : STG_O;
+  // chunk c of a frame -> kind, first column (in the concatenated Q|V|K space for projections), width (128 or 64)
+  static constexpr int kind_of(int c) { return c < NPC ? CK_PROJ : c == C_S ? CK_S : c < C_O ? CK_AV : CK_O; }
+  static constexpr int col0_of(int c) { return kind_of(c) == CK_PROJ ? c * 128 : kind_of(c) == CK_AV ? (c - C_AV0) * 128 : 0; }
+  static constexpr int ncols_of(int c) {
+    const int k = kind_of(c);
+    const int left = k == CK_PROJ ? PW - c * 128 : k == CK_AV ? P - (c - C_AV0) * 128 : k == CK_S ? S : E;
+    return left < 128 ? left : 128;
   }
-  static constexpr int idx_of(int c) {
-    return c < 3 * NQ ? c % NQ : c < 3 * NQ + 2 ? c - 3 * NQ : c < 4 * NQ + 2 ? c - 3 * NQ - 2 : c - 4 * NQ - 2;
+  // Both epilogue warpgroups of the slot drain every chunk: warpgroup w takes the sub-block [w * SW, (w + 1) * SW) of the
+  // chunk's columns, SW = ncols / 2 (64 or 32).  A sub-block never straddles two stages (P is a multiple of 64).
+  static constexpr int sub_w(int c) { return ncols_of(c) / 2; }
+  static constexpr int stage_at(int c, int col) {                        // stage that owns column `col` of chunk c
+    const int k = kind_of(c);
+    if (k != CK_PROJ) return k == CK_S ? STG_S : k == CK_AV ? STG_AV : STG_O;
+    const int gc = c * 128 + (col < ncols_of(c) ? col : 0);
+    return gc < P ? STG_Q : gc < 2 * P ? STG_V : STG_K;
   }
-  static constexpr int ncols_of(int c) { return stage_of(c) == STG_O ? OC : 64; }
-  static constexpr int col0_of(int c) { return idx_of(c) * ncols_of(c); }
-  // which epilogue warpgroup of the slot drains chunk c: 0 = A (owns the logits), 1 = B
-  static constexpr int wg_of(int c) {
-    const int st = stage_of(c);
-    if (st == STG_S) return idx_of(c);                                   // keys 0..63 -> A, keys 64..127 -> B
-    if (c < 3 * NQ) return c % 2;                                        // projections: alternate
-    if (st == STG_AV) return idx_of(c) % 2;
-    return idx_of(c) == 0 ? 1 : 0;                                       // O0 -> B, O1 -> A
+  static constexpr int stage_of(int c, int w) { return stage_at(c, w * sub_w(c)); }
+  static constexpr int stage_col0(int c, int w) {                        // first column of the sub-block inside its stage's matrix
+    const int gc = col0_of(c) + w * sub_w(c);
+    return kind_of(c) == CK_PROJ ? gc % P : gc;
   }
   // arrivals (warps) that complete a stage's "operand written" barrier
-  static constexpr int dep_count(int stage) { return (stage == STG_S ? 2 : NQ) * 4; }
-  static constexpr int S0_CHUNK = 3 * NQ;
-  // The MMA thread needs region c%4 drained by its previous user p = c-4 (previous frame if negative).  The drain is
-  // implied when the thread has already waited for the "operand written" barrier of p's stage (the epilogue arrives
-  // there after its TMEM loads): Q/K at S0, V/S at AV0, AV at O0.  Output-projection chunks have no such barrier.
-  static constexpr int dep_wait_chunk(int stage) {
-    return (stage == STG_Q || stage == STG_K) ? 3 * NQ : (stage == STG_V || stage == STG_S) ? 3 * NQ + 2 : 4 * NQ + 2;
-  }
-  static constexpr bool needs_empty_wait(int c) {
-    const int p = (c + NCH - kRegions) % NCH;
-    const int sp = stage_of(p);
-    if (sp == STG_O) return true;
-    return p < c ? dep_wait_chunk(sp) > c : false;
+  static constexpr int dep_count(int stage) {
+    int n = 0;
+    for (int c = 0; c < NCH; ++c)
+      for (int w = 0; w < 2; ++w) n += stage_of(c, w) == stage ? 4 : 0;
+    return n;
   }
 };
 
 // ------------------------------------------------------------------------------- requantisation on the FMA pipe (RQM_FP)
 // The integer forms below cost the two scarce pipes (IMAD.HI: 4 fmaheavy cycles per warp; IMAD + SHF: fmaheavy + alu).
 // RQM_FP moves the multiply, the rounding and the shift of  y = ((acc*mult + rnd) >> shift) + add  into ONE FFMA.RM:
-//   * the epilogue that drains an accumulator region presets it (tcgen05.st) to INIT for its next user, and every MMA
-//     accumulates, so TMEM holds bits = INIT + acc with 0 < bits < 2^24.  Read as an f32 such a pattern (exponent field 0
-//     or 1) is exactly bits * 2^-149;
+//   * the digit K steps add a per-stage offset INIT > |acc|max on the tensor pipe (unsigned radix-255 digits against the
+//     constant tile: folded into the bias digits of the projections, two extra steps for Q.K^T, one for A.V), so TMEM holds
+//     bits = INIT + acc with 0 < bits < 2^24.  Read as an f32 such a pattern (exponent field 0 or 1) is exactly bits * 2^-149;
 //   * INIT is chosen per stage with INIT*mult == rnd (mod 2^shift), so C = (rnd - INIT*mult)/2^shift + add + 128 is an
 //     integer and  fma.rm(bits_f32, mult*2^-shift, C*2^-149)  has the exact value ((acc*mult + rnd)/2^shift + add + 128) * 2^-149;
 //     rounding toward -inf at the denormal ulp is the floor, so the result's BIT PATTERN is y + 128 when that is >= 0 and
@@ -171,7 +176,9 @@ struct Cfg {
 //   * cvt.pack.sat.u8.s32 of the bit patterns clamps to [0, 255] = sat_s8(y) + 128, and one XOR 0x80808080 per four
 //     elements turns that into s8.  (Checked exhaustively over +-4.3M accumulators x 59 parameter sets on B200:
 //     tools/fp_requant_check.cu.)
-// The ITAmax distance m - a = ceil((m + 128 - C) - bits*mult*2^-shift) is one FFMA.RP the same way.
+// The ITAmax distance m - a + 1 = ceil((m + 129 - C) - bits*mult*2^-shift) is one FFMA.RP the same way.
+// (A first version preset the accumulators with tcgen05.st instead: a store needs distinct source registers, i.e. one
+//  register copy per column, which cost more than the FFMA saved.)
 // ---------------------------------------------------------------------------------------------------- requant forms
 // ALT selects how INT_HI elements are computed: 0 = one IMAD.HI each; 1 = 32-bit IMAD + SHF each; 2 = alternate (even
 // elements IMAD.HI, odd elements 32-bit) to balance the fma pipe (IMAD.HI occupies it twice as long) against issue slots.
@@ -223,11 +230,14 @@ __device__ __forceinline__ uint32_t shr_clamp(uint32_t v, uint32_t s) {   // PTX
 }
 
 #ifdef ITA_TRACE
-// Developer builds: [warp][iteration < 8, 8 = sink][chunk][4] SM clock stamps of CTA 0.  Branch-free (every lane stores to
-// the same word; launches that are not traced still get a buffer), so a stamp is CS2R + STG.
+// Developer builds: [warp][iteration < 8][chunk][4] SM clock stamps of CTA 0 (every lane stores to the same word; the
+// condition is warp-uniform; launches that are not traced still get a buffer).
 constexpr int kTraceIters = 8;
 #define ITA_TR(prm, warp, it, c, k)                                                                                          \
-  (prm).trace[((((long long)(warp)) * (kTraceIters + 1) + ((blockIdx.x == 0 && (it) < kTraceIters) ? (it) : kTraceIters)) * 32 + (c)) * 4 + (k)] = clock64()
+  do {                                                                                                                       \
+    if (blockIdx.x == 0 && (it) < kTraceIters)   /* warp-uniform: a predicated store, no divergence */                      \
+      (prm).trace[((((long long)(warp)) * (kTraceIters + 1) + (it)) * 32 + (c)) * 4 + (k)] = clock64();                      \
+  } while (0)
 #else
 #define ITA_TR(prm, warp, it, c, k) do { } while (0)
 #endif
@@ -267,7 +277,7 @@ __device__ __forceinline__ void tmem_pin32(uint32_t (&v)[32]) {
 // Walk NG groups of 32 accumulator columns of this thread's row, software-pipelined: the TMEM load of group g+1 is in
 // flight while f(g, v) works on group g.  addr(g) gives the TMEM address of group g.  After the last load has landed,
 // `done.issue()` runs once, and `done.finish()` after the last group has been processed (together they hand the TMEM
-// region back to the MMA thread; the split lets the RQM_FP preset stores overlap the last group's arithmetic).
+// region back to the MMA thread).
 struct NoRelease {
   __device__ __forceinline__ void issue() const {}
   __device__ __forceinline__ void finish() const {}
@@ -285,6 +295,18 @@ __device__ __forceinline__ Release<I, Fn> make_release(I i, Fn f) { return Relea
 template <int NG, class A, class F, class D>
 __device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
   uint32_t va[32], vb[32];
+#if defined(ITA_EXP_NOLD)      // timing experiment (wrong results): no TMEM reads
+#pragma unroll
+  for (int i = 0; i < 32; ++i) va[i] = vb[i] = addr(0) + i;
+  tmem_pin32(va);
+  tmem_pin32(vb);
+  static_for<0, NG>([&](auto gg) {
+    constexpr int g = decltype(gg)::value;
+    if constexpr (g + 1 == NG) done.issue();
+    f(gg, (g & 1) ? vb : va);
+    if constexpr (g + 1 == NG) done.finish();
+  });
+#else
   tmem_ld32(addr(0), va);
   tmem_wait32(va);
   static_for<0, NG>([&](auto gg) {
@@ -296,10 +318,15 @@ __device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
       tmem_pin32(cur);              // keeps the compiler from hoisting the work on `cur` above the load just issued
     }
     if constexpr (g + 1 == NG) done.issue();
+#if defined(ITA_EXP_NOMATH)    // timing experiment (wrong results): TMEM reads and synchronisation only
+    if (cur[0] == 0x12345678u && cur[31] == 0x9abcdef0u) f(gg, cur);
+#else
     f(gg, cur);
+#endif
     if constexpr (g + 1 < NG) tmem_wait32(nxt);
     if constexpr (g + 1 == NG) done.finish();
   });
+#endif
 }
 
 // Requantise 32 accumulators of one row -> int8 -> panel buffer (and/or global).
@@ -646,7 +673,7 @@ __device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, in
 }
 
 // ---------------------------------------------------------------------------------------------------- epilogue warps
-// One warpgroup (WG = 0: "A", 1: "B") of one slot: drains the chunks Cfg::wg_of assigns to it, in chunk order.  The chunk
+// One warpgroup (WG = 0: "A", 1: "B") of one slot: drains its sub-block of every chunk, in chunk order.  The chunk
 // schedule is unrolled at compile time: a lone warp issues one dependent instruction every ~5 cycles, so run-time chunk
 // bookkeeping (tried: a run-time loop over three code paths) costs more than the instruction-cache misses it saves.
 template <int E, int P, int MODE, int SOFTMAX, int ALT, bool DUMP, int WG>
@@ -658,94 +685,66 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
   int8_t *const q_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_Q, *const k_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_K,
                *const v_buf = reinterpret_cast<int8_t *>(sc.smem) + C::OFF_V;
   bool ok = true;
-  if constexpr (MODE == RQM_FP && WG == 0) {
-    // preset the accumulator ring for the first kRegions chunks (phase 0 of the EMPTY barriers)
-    static_for<0, kRegions>([&](auto rr) {
-      constexpr int r = decltype(rr)::value;
-      const uint32_t v = (uint32_t)prm.rq[C::stage_of(r)].init;
-      tmem_fill32(t_lane + r * kRegionCols, v);
-      tmem_fill32(t_lane + r * kRegionCols + 32, v);
-    });
-    tmem_st_wait();
-    tc_fence_before();
-    __syncwarp();
-    if (lane == 0)
-      for (int r = 0; r < kRegions; ++r) mbar_arrive(sc.bars + BAR_EMPTY + r);
-  }
+  uint32_t n = 0;                                   // running chunk number: region n & 1, its (n >> 1)-th use
   for (long long it = 0; it < iters && ok; ++it) {
     const long long f = frame0 + it * frame_stride;
     static_for<0, C::NCH>([&](auto cc) {
       constexpr int c = decltype(cc)::value;
-      constexpr int stage = C::stage_of(c), idx = C::idx_of(c), NC = C::ncols_of(c), col0 = C::col0_of(c), r = c % kRegions;
-      if constexpr (C::wg_of(c) == WG) {
-        if (!ok) return;
-        const uint32_t use = (uint32_t)(it * (C::NCH / kRegions)) + c / kRegions;
-        ITA_TR(prm, threadIdx.x >> 5, it, c, 0);
-        ok = mbar_wait(sc.bars + BAR_FULL + r, use & 1, prm.abort_flag);
-        if (!ok) return;
-        ITA_TR(prm, threadIdx.x >> 5, it, c, 1);
-        tc_fence_after();
-        const uint32_t taddr = t_lane + r * kRegionCols;
-        // hand the region back: (RQM_FP: preset it for its next user, chunk c + kRegions, first) then arrive on EMPTY
-        auto release = make_release(
-            [&] {
-              if constexpr (MODE == RQM_FP) {
-                const uint32_t v = (uint32_t)prm.rq[C::stage_of((c + kRegions) % C::NCH)].init;
-                tmem_fill32(taddr, v);
-                tmem_fill32(taddr + 32, v);
-              } else {
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(sc.bars + BAR_EMPTY + r);
-                ITA_TR(prm, threadIdx.x >> 5, it, c, 2);
-              }
-            },
-            [&] {
-              if constexpr (MODE == RQM_FP) {
-                tmem_st_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(sc.bars + BAR_EMPTY + r);
-                ITA_TR(prm, threadIdx.x >> 5, it, c, 2);
-              }
-            });
-        if constexpr (stage == STG_S) {
-          // ---- logits: this warpgroup's 64 key columns -> ITAmax -> Asm (u8) into the K buffer
-          int8_t *gA = nullptr;
-          uint8_t *gAsm = nullptr;
-          if constexpr (DUMP) {
-            if (prm.dA) gA = prm.dA + (f * kS + row) * kS;
-            if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
-          }
-          if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && MODE == RQM_FP)
-            itamax_repo_half_fp<DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
-          else if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
-            itamax_repo_half<MODE, ALT, DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
-          else
-            itamax_stream_half<MODE, DUMP, idx>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
-        } else {
-          int8_t *panel = stage == STG_Q ? q_buf : stage == STG_K ? k_buf : stage == STG_V ? v_buf : stage == STG_AV ? q_buf : nullptr;
-          int8_t *g = nullptr;
-          if constexpr (stage == STG_O) {
-            g = prm.y + (f * kS + row) * E + col0;
-          } else if constexpr (DUMP) {
-            int8_t *base = stage == STG_Q ? prm.dQ : stage == STG_K ? prm.dK : stage == STG_V ? prm.dV : prm.dO;
-            if (base) g = base + (f * kS + row) * P + col0;
-          }
-          tmem_walk<NC / 32>([&](int gi) { return taddr + (uint32_t)gi * 32u; },
-                             [&](auto gg, const uint32_t(&v)[32]) {
-                               constexpr int gi = decltype(gg)::value;
-                               requant_store32<MODE, ALT>(v, prm.rq[stage], panel, row, col0 + gi * 32, g ? g + gi * 32 : nullptr);
-                             },
-                             release);
+      constexpr int kind = C::kind_of(c), SW = C::sub_w(c), stage = C::stage_of(c, WG), col0 = C::stage_col0(c, WG);
+      if (!ok) return;
+      const uint32_t r = n & 1u, use = n >> 1;
+      ++n;
+      ITA_TR(prm, threadIdx.x >> 5, it, c, 0);
+      ok = mbar_wait(sc.bars + BAR_FULL + r, use & 1, prm.abort_flag);
+      if (!ok) return;
+      ITA_TR(prm, threadIdx.x >> 5, it, c, 1);
+      tc_fence_after();
+      const uint32_t taddr = t_lane + r * kRegionCols + WG * SW;
+      // hand the region back as soon as this warp's last load has landed
+      auto release = make_release(
+          [&] {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sc.bars + BAR_EMPTY + r);
+            ITA_TR(prm, threadIdx.x >> 5, it, c, 2);
+          },
+          [] {});
+      if constexpr (kind == CK_S) {
+        // ---- logits: this warpgroup's 64 key columns -> ITAmax -> Asm (u8) into the K buffer
+        int8_t *gA = nullptr;
+        uint8_t *gAsm = nullptr;
+        if constexpr (DUMP) {
+          if (prm.dA) gA = prm.dA + (f * kS + row) * kS;
+          if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
         }
-        if constexpr (stage != STG_O) {
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(sc.bars + BAR_DEP + stage);
+        if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && MODE == RQM_FP)
+          itamax_repo_half_fp<DUMP, WG>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+        else if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
+          itamax_repo_half<MODE, ALT, DUMP, WG>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+        else
+          itamax_stream_half<MODE, DUMP, WG>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+      } else {
+        int8_t *panel = stage == STG_Q ? q_buf : stage == STG_K ? k_buf : stage == STG_V ? v_buf : stage == STG_AV ? q_buf : nullptr;
+        int8_t *g = nullptr;
+        if constexpr (stage == STG_O) {
+          g = prm.y + (f * kS + row) * E + col0;
+        } else if constexpr (DUMP) {
+          int8_t *base = stage == STG_Q ? prm.dQ : stage == STG_K ? prm.dK : stage == STG_V ? prm.dV : prm.dO;
+          if (base) g = base + (f * kS + row) * P + col0;
         }
-        ITA_TR(prm, threadIdx.x >> 5, it, c, 3);
+        tmem_walk<SW / 32>([&](int gi) { return taddr + (uint32_t)gi * 32u; },
+                           [&](auto gg, const uint32_t(&v)[32]) {
+                             constexpr int gi = decltype(gg)::value;
+                             requant_store32<MODE, ALT>(v, prm.rq[stage], panel, row, col0 + gi * 32, g ? g + gi * 32 : nullptr);
+                           },
+                           release);
       }
+      if constexpr (stage != STG_O) {
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(sc.bars + BAR_DEP + stage);
+      }
+      ITA_TR(prm, threadIdx.x >> 5, it, c, 3);
     });
   }
 }
@@ -778,7 +777,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
       mbar_init(b + BAR_XFREE, 1);
       for (int r = 0; r < kRegions; ++r) {
         mbar_init(b + BAR_FULL + r, 1);
-        mbar_init(b + BAR_EMPTY + r, 4);
+        mbar_init(b + BAR_EMPTY + r, kEpiWarpsPerSlot);
       }
       for (int st = STG_Q; st <= STG_AV; ++st) mbar_init(b + BAR_DEP + st, C::dep_count(st));
     }
@@ -827,80 +826,84 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
       const bool leader = elect_one();
       uint64_t *b = slot_bars + slot * kBarsPerSlot;
       bool ok = mbar_wait(bar_w, 0, prm.abort_flag);
-      // instruction descriptors (M = 128)
-      constexpr uint32_t ID_PROJ = make_idesc_i8(kS, 64, 1, 1, 0, 0);      // X . W^T           64 of the P columns
-      constexpr uint32_t ID_QK = make_idesc_i8(kS, 64, 1, 1, 0, 0);        // Q . K^T           64 key columns
-      constexpr uint32_t ID_AV = make_idesc_i8(kS, 64, 0, 1, 0, 1);        // Asm(u8) . V       64 of the P columns, B MN-major
-      constexpr uint32_t ID_O = make_idesc_i8(kS, C::OC, 1, 1, 0, 0);      // O . Wo            E/2 columns
       // operand buffer addresses in 16-byte units (the descriptor address field)
       const uint32_t w16 = smem_u32(smem + C::OFF_W) >> 4;
-      const uint32_t ones16 = smem_u32(smem + C::OFF_ONES) >> 4;
+      const uint32_t ca16 = smem_u32(smem + C::OFF_CA) >> 4, dqk16 = smem_u32(smem + C::OFF_DQK) >> 4, dav16 = smem_u32(smem + C::OFF_DAV) >> 4;
       const uint32_t slot16 = smem_u32(smem + C::OFF_SLOT + slot * C::SLOT_BYTES) >> 4;
       const uint32_t x16 = slot16 + (C::OFF_X >> 4), q16 = slot16 + (C::OFF_Q >> 4), k16 = slot16 + (C::OFF_K >> 4),
                      v16 = slot16 + (C::OFF_V >> 4);
       const uint32_t d_base = tmem_base + slot * kTmemColsPerSlot;
+      uint32_t n = 0;                                 // running chunk number: region n & 1, its (n >> 1)-th use
       for (long long it = 0; it < iters && ok; ++it) {
         const uint32_t ph = (uint32_t)(it & 1);
         static_for<0, C::NCH>([&](auto cc) {
           constexpr int c = decltype(cc)::value;
-          constexpr int stage = C::stage_of(c), idx = C::idx_of(c), r = c % kRegions;
+          constexpr int kind = C::kind_of(c), col0 = C::col0_of(c), NC = C::ncols_of(c);
           if (!ok) return;
-          const uint32_t use = (uint32_t)(it * (C::NCH / kRegions)) + c / kRegions;
+          const uint32_t r = n & 1u, use = n >> 1;
+          ++n;
           ITA_TR(prm, warp, it, c, 0);
-          if constexpr (MODE == RQM_FP) {
-            // EMPTY phase `use` = "region preset for its use-th user" (phase 0: the initial preset)
-            if (C::needs_empty_wait(c) || use == 0) ok = mbar_wait(b + BAR_EMPTY + r, use & 1, prm.abort_flag);
-          } else if constexpr (C::needs_empty_wait(c)) {
-            if (use > 0) ok = mbar_wait(b + BAR_EMPTY + r, (use - 1) & 1, prm.abort_flag);
-          }
+          if (use > 0) ok = mbar_wait(b + BAR_EMPTY + r, (use - 1) & 1, prm.abort_flag);
           ITA_TR(prm, warp, it, c, 1);
-          if constexpr (idx == 0) {
-            if constexpr (stage == STG_Q) ok = ok && mbar_wait(b + BAR_X, ph, prm.abort_flag);
-            if constexpr (stage == STG_S) ok = ok && mbar_wait(b + BAR_DEP + STG_Q, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_K, ph, prm.abort_flag);
-            if constexpr (stage == STG_AV) ok = ok && mbar_wait(b + BAR_DEP + STG_V, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_S, ph, prm.abort_flag);
-            if constexpr (stage == STG_O) ok = ok && mbar_wait(b + BAR_DEP + STG_AV, ph, prm.abort_flag);
-          }
+          if constexpr (c == 0) ok = ok && mbar_wait(b + BAR_X, ph, prm.abort_flag);
+          if constexpr (c == C::C_S) ok = ok && mbar_wait(b + BAR_DEP + STG_Q, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_K, ph, prm.abort_flag);
+          if constexpr (c == C::C_AV0) ok = ok && mbar_wait(b + BAR_DEP + STG_V, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_S, ph, prm.abort_flag);
+          if constexpr (c == C::C_O) ok = ok && mbar_wait(b + BAR_DEP + STG_AV, ph, prm.abort_flag);
           if (!ok) return;
           tc_fence_after();
           ITA_TR(prm, warp, it, c, 2);
           const uint32_t d_tmem = d_base + r * kRegionCols;
-          constexpr uint32_t acc0 = MODE == RQM_FP ? 1u : 0u;        // RQM_FP: the region is preset, every MMA accumulates
+          // digit K steps: s8 digits against [1, 127, ...] (integer forms) or u8 digits against [1, 255, ...] (RQM_FP)
+          constexpr int DSG = MODE == RQM_FP ? 0 : 1;
           if (leader) {
-            if constexpr (stage <= STG_V) {
-              // projections: A = X [S rows, K = E] K-major; B = rows [64 idx, +64) of W_t^T [P rows, K = E + 32] K-major;
-              // the last K step multiplies the constant tile with the bias digits
-              constexpr uint32_t wt = stage * C::WA_BYTES + idx * 64 * 16;
+            if constexpr (kind == CK_PROJ) {
+              // projections: A = X [S rows, K = E] K-major; B = rows [col0, +NC) of [Wq | Wv | Wk]^T [3P rows, K = E + 32]
+              // K-major; the last K step multiplies the constant tile with the bias (+ offset) digits
+              constexpr uint32_t ID = make_idesc_i8(kS, NC, 1, 1, 0, 0), IDD = make_idesc_i8(kS, NC, DSG, DSG, 0, 0);
+              constexpr uint32_t wt = col0 * 16;
 #pragma unroll
               for (int k = 0; k < E / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(x16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(w16, wt + k * 2 * P * 16, P * 16, 128), ID_PROJ, k > 0 ? 1u : acc0);
-              umma_i8(d_tmem, make_smem_desc_rel(ones16, 0, kS * 16, 128), make_smem_desc_rel(w16, wt + (E / 16) * P * 16, P * 16, 128),
-                      ID_PROJ, 1);
-            } else if constexpr (stage == STG_S) {
-              // logits: A = Q [S, K = P] K-major; B = rows (keys) [64 idx, +64) of K [S rows, K = P] K-major
+                        make_smem_desc_rel(w16, wt + k * 2 * C::PW * 16, C::PW * 16, 128), ID, k > 0);
+              umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, wt + (E / 16) * C::PW * 16, C::PW * 16, 128),
+                      IDD, 1);
+            } else if constexpr (kind == CK_S) {
+              // logits: A = Q [S, K = P] K-major; B = K [S rows (keys), K = P] K-major; RQM_FP: + two offset steps
+              constexpr uint32_t ID = make_idesc_i8(kS, kS, 1, 1, 0, 0), IDD = make_idesc_i8(kS, kS, 0, 0, 0, 0);
 #pragma unroll
               for (int k = 0; k < P / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(k16, idx * 64 * 16 + k * 2 * kS * 16, kS * 16, 128), ID_QK, k > 0 ? 1u : acc0);
-            } else if constexpr (stage == STG_AV) {
-              // context: A = Asm [S, K = S] u8 K-major (in the K buffer); B = columns [64 idx, +64) of V [K = S rows, N = P] MN-major
+                        make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128), ID, k > 0);
+              if constexpr (MODE == RQM_FP) {
+                umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dqk16, 0, 128, 0), IDD, 1);
+                umma_i8(d_tmem, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(dqk16, 256, 128, 0), IDD, 1);
+              }
+            } else if constexpr (kind == CK_AV) {
+              // context: A = Asm [S, K = S] u8 K-major (in the K buffer); B = columns [col0, +NC) of V [K = S rows, N = P]
+              // MN-major; RQM_FP: + one offset step
+              constexpr uint32_t ID = make_idesc_i8(kS, NC, 0, 1, 0, 1), IDD = make_idesc_i8(kS, NC, 0, 0, 0, 0);
 #pragma unroll
               for (int k = 0; k < kS / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(v16, idx * 4 * kS * 16 + k * 32 * 16, 128, kS * 16), ID_AV, k > 0 ? 1u : acc0);
+                        make_smem_desc_rel(v16, (col0 / 16) * kS * 16 + k * 32 * 16, 128, kS * 16), ID, k > 0);
+              if constexpr (MODE == RQM_FP) umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dav16, 0, 128, 0), IDD, 1);
             } else {
-              // output projection: A = O [S, K = P] K-major (in the Q buffer); B = rows [OC idx, +OC) of Wo^T [E rows, K = P + 32]
-              constexpr uint32_t wo = 3 * C::WA_BYTES + idx * C::OC * 16;
+              // output projection: A = O [S, K = P] K-major (in the Q buffer); B = Wo^T [E rows, K = P + 64]; one digit step
+              // (integer forms) or two (RQM_FP)
+              constexpr uint32_t ID = make_idesc_i8(kS, E, 1, 1, 0, 0), IDD = make_idesc_i8(kS, E, DSG, DSG, 0, 0);
+              constexpr uint32_t wo = C::OFF_WO;
 #pragma unroll
               for (int k = 0; k < P / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128), make_smem_desc_rel(w16, wo + k * 2 * E * 16, E * 16, 128),
-                        ID_O, k > 0 ? 1u : acc0);
-              umma_i8(d_tmem, make_smem_desc_rel(ones16, 0, kS * 16, 128), make_smem_desc_rel(w16, wo + (P / 16) * E * 16, E * 16, 128), ID_O, 1);
+                        ID, k > 0);
+              umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, wo + (P / 16) * E * 16, E * 16, 128), IDD, 1);
+              if constexpr (MODE == RQM_FP)
+                umma_i8(d_tmem, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(w16, wo + (P / 16 + 2) * E * 16, E * 16, 128), IDD, 1);
             }
             umma_commit(b + BAR_FULL + r);
             // the X buffer may be overwritten once its last reader is complete: the last projection, or -- when X shares
-            // storage with the K columns beyond the softmax output -- the last logits MMA
-            if constexpr (C::X_IN_KTAIL ? (stage == STG_S && idx == 1) : (c == 3 * C::NQ - 1)) umma_commit(b + BAR_XFREE);
+            // storage with the K columns beyond the softmax output -- the logits MMA
+            if constexpr (C::X_IN_KTAIL ? (c == C::C_S) : (c == C::NPC - 1)) umma_commit(b + BAR_XFREE);
           }
           __syncwarp();
           ITA_TR(prm, warp, it, c, 3);

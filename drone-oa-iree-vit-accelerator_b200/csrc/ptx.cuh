@@ -176,16 +176,6 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
-// 32 lanes x 32 consecutive columns <- one value (every thread writes `v` into its row, columns col..col+31)
-__device__ __forceinline__ void tmem_fill32(uint32_t taddr, uint32_t v) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-      "{%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, "
-      "%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};\n" ::"r"(taddr),
-      "r"(v)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------------- descriptors
 // Shared-memory matrix descriptor, SWIZZLE_NONE ("interleave") canonical layout: the operand is stored as 8x16-byte core

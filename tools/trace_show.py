@@ -3,8 +3,9 @@ import sys
 import numpy as np
 t = np.fromfile(sys.argv[1], dtype=np.int64).reshape(19, 9, 32, 4)
 NQ = 3
-names = ["Q0", "Q1", "Q2", "V0", "V1", "V2", "K0", "K1", "K2", "S0", "S1", "AV0", "AV1", "AV2", "O0", "O1"]
+names = ["P0", "P1", "P2", "P3", "P4", "S", "AV0", "AV1", "O"]
 it = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+WG = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 for slot in (0, 1):
     mma = 16 + slot
     base = t[mma, it, 0, 0]
@@ -15,7 +16,7 @@ for slot in (0, 1):
         m = t[mma, it, c] - base
         row = None
         for w in range(slot * 8, slot * 8 + 8):
-            if t[w, it, c, 1] != 0 and (w & 3) == 0 and row is None:
+            if t[w, it, c, 1] != 0 and (w & 3) == 0 and (w >> 2) % 2 == WG and row is None:
                 row = (w, t[w, it, c] - base)
         if row is None:
             print(f"{nm:6s} | {m[0]:6d} {m[1]:6d} {m[2]:6d} {m[3]:6d} |   (S1 handled with S0)")
