@@ -13,21 +13,25 @@
 //     V [S,P] -> B operand of A.V (MN-major: rows are K) Asm [S,S] u8 -> A operand of A.V     O [S,P] -> A operand of O.Wo
 //   Weights are pre-arranged on the host into the same panel layout (W^T as [N rows, K cols]) and bulk-copied once per CTA.
 //
-// Biases ride on the tensor pipe: every weight matrix carries 32 extra K columns holding the int32 bias of its output
-// column as signed base-127 digits (b = g0 + 127 * (g1 + ... + g31)), and the matching A operand of that extra K step
-// is a constant tile whose rows are [1, 127, ..., 127].  The accumulator that reaches the epilogue already contains
-// the bias, so requantisation needs only per-stage *uniform* constants (no per-column loads).
+// Biases ride on the tensor pipe: every weight matrix carries extra K columns holding the int32 bias of its output
+// column as base-R digits (b = g0 + R * (g1 + ... + g31)), and the matching A operand of that extra K step is a constant
+// tile whose rows are [1, R, ..., R] (8 rows in shared memory, SBO = 0 so that every row group of the operand reads them).
+// The accumulator that reaches the epilogue already contains the bias, so requantisation needs only per-stage *uniform*
+// constants (no per-column loads).  R = 127 with signed digits for the integer requant forms, 255 with unsigned digits
+// for RQM_FP, where the digits also carry the stage's accumulator offset (see "requantisation on the FMA pipe").
 //
-// Pipeline.  A frame is cut into NCH = 4*P/64 + 4 "chunks", each one accumulator tile of <= 64 columns, in the order
-//     Q[0..NQ) V[0..NQ) K[0..NQ)  S0 S1  AV[0..NQ)  O0 O1            (NQ = P/64; S chunks are 64 key columns, O chunks E/2)
-//   Two frames ("slots") are in flight per SM.  Per slot, TMEM holds a ring of 4 regions x 64 columns; chunk c uses
-//   region c%4.  Each slot has two epilogue warpgroups (4 warps = the 4 TMEM lane quadrants): warpgroup A owns the
-//   logits (both S chunks: a thread holds a whole 128-column row, so ITAmax needs no cross-thread exchange) plus a
-//   share of the other chunks, warpgroup B the rest (Cfg::wg_of).  One MMA-issuing thread per slot walks the chunks in
-//   order, waiting only for (a) the region to be drained and (b) the operand buffers of the chunk to be written
-//   (mbarriers armed by the producing epilogues); a loader thread prefetches the next frame's X tile by TMA.  tcgen05
-//   MMAs of one thread complete in issue order, which is what makes the reuse of the operand buffers (Asm over K, O
-//   over Q, the next X tile in the unused tail of the K buffer) safe.
+// Pipeline.  The three projections are ONE GEMM against the concatenated weights [Wq | Wv | Wk] (3P output columns).  A
+// frame is cut into NCH "chunks", each one accumulator tile of 128 (or a trailing 64) columns, in the order
+//     P[0..NPC)  S  AV[0..NAVC)  O           (NPC = ceil(3P/128), S = all 128 keys, NAVC = ceil(P/128), O = E columns)
+//   Two frames ("slots") are in flight per SM.  Per slot, TMEM holds a ring of 2 regions x 128 columns; the n-th chunk
+//   of the slot uses region n % 2.  Each slot has two epilogue warpgroups (4 warps = the 4 TMEM lane quadrants); BOTH drain
+//   every chunk, warpgroup w taking the sub-block [w*SW, (w+1)*SW) of its columns (SW = 64 or 32).  For the logits that
+//   means a thread of warpgroup A holds keys 0..63 of its row and its twin in warpgroup B keys 64..127; they exchange the
+//   row max / row sum through shared memory.  One MMA-issuing thread per slot walks the chunks in order, waiting only for
+//   (a) the region to be drained and (b) the operand buffers of the chunk to be written (mbarriers armed by the
+//   producing epilogues); a loader thread prefetches the next frame's X tile by TMA.  tcgen05 MMAs of one thread complete
+//   in issue order, which is what makes the reuse of the operand buffers (Asm over K, O over Q, the next X tile in the
+//   unused tail of the K buffer) safe.  The two slots are kept out of phase (BAR_TURN).
 //
 // Thread roles (608 threads): warps 0-7 = epilogue of slot 0 (warp w: TMEM lanes 32*(w%4).., warpgroup (w/4)%2),
 // warps 8-15 = slot 1, warps 16/17 = MMA issue for slot 0/1 (one elected thread), warp 18 = TMA loader + TMEM allocator.
@@ -69,7 +73,7 @@ constexpr int kConstBytes = kConstABytes + kConstQKBytes + kConstAVBytes;
 enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2, RQM_FP = 3 };
 enum { STG_Q = 0, STG_K, STG_V, STG_S, STG_AV, STG_O };
 // per-slot mbarriers
-enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2 /* + region */, BAR_EMPTY = 4 /* + region */, BAR_DEP = 6 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */ };
+enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2 /* + region */, BAR_EMPTY = 4 /* + region */, BAR_DEP = 6 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */, BAR_TURN = 11 };
 enum { CK_PROJ = 0, CK_S, CK_AV, CK_O };   // chunk kinds
 
 // Per-stage uniform requant parameters as the fused kernel consumes them.
@@ -109,6 +113,7 @@ struct Cfg {
   static constexpr int NAVC = (P + 127) / 128;                           // A.V chunks
   static constexpr int NCH = NPC + NAVC + 2;                             // + logits + output projection
   static constexpr int C_S = NPC, C_AV0 = NPC + 1, C_O = NPC + 1 + NAVC;
+  static constexpr int C_TURN = NPC >= 3 ? 2 : NPC - 1;                  // chunk whose issue lets the other slot start its frame
   static constexpr int WP_BYTES = PW * (E + kBiasK);                     // [Wq | Wv | Wk]^T with bias digits
   static constexpr int WO_BYTES = E * (P + kBiasKO);                     // Wo^T with bias digits
   static constexpr int OFF_W = 0;
@@ -780,6 +785,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
         mbar_init(b + BAR_EMPTY + r, kEpiWarpsPerSlot);
       }
       for (int st = STG_Q; st <= STG_AV; ++st) mbar_init(b + BAR_DEP + st, C::dep_count(st));
+      mbar_init(b + BAR_TURN, 1);
     }
     fence_mbar_init();
   }
@@ -843,6 +849,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
           const uint32_t r = n & 1u, use = n >> 1;
           ++n;
           ITA_TR(prm, warp, it, c, 0);
+          // Keep the two slots out of phase: a slot starts a frame only after the other slot has issued chunk C_TURN of its
+          // previous turn (slot 1: of the same iteration, slot 0: of the iteration before).  Left alone the slots fall into
+          // lockstep (measured), where both sit in the same MMA-latency bubbles and the same epilogue bursts; out of phase
+          // one slot's arithmetic fills the other's waits (+11 % measured).
+          if constexpr (c == 0) {
+            uint64_t *other = slot_bars + (slot ^ 1) * kBarsPerSlot + BAR_TURN;
+            if (slot == 1) ok = mbar_wait(other, ph, prm.abort_flag);
+            else if (it > 0 && it - 1 < iters_of(1)) ok = mbar_wait(other, ph ^ 1u, prm.abort_flag);
+            if (!ok) return;
+          }
           if (use > 0) ok = mbar_wait(b + BAR_EMPTY + r, (use - 1) & 1, prm.abort_flag);
           ITA_TR(prm, warp, it, c, 1);
           if constexpr (c == 0) ok = ok && mbar_wait(b + BAR_X, ph, prm.abort_flag);
@@ -901,6 +917,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
                 umma_i8(d_tmem, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(w16, wo + (P / 16 + 2) * E * 16, E * 16, 128), IDD, 1);
             }
             umma_commit(b + BAR_FULL + r);
+            if constexpr (c == C::C_TURN) mbar_arrive(b + BAR_TURN);
             // the X buffer may be overwritten once its last reader is complete: the last projection, or -- when X shares
             // storage with the K columns beyond the softmax output -- the logits MMA
             if constexpr (C::X_IN_KTAIL ? (c == C::C_S) : (c == C::NPC - 1)) umma_commit(b + BAR_XFREE);
