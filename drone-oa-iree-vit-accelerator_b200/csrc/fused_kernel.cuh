@@ -861,6 +861,29 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
           }
           if (use > 0) ok = mbar_wait(b + BAR_EMPTY + r, (use - 1) & 1, prm.abort_flag);
           ITA_TR(prm, warp, it, c, 1);
+          // The digit K steps of the logits, the context and the output projection read only constants: they go first
+          // (overwriting the region) and run while this thread still waits for the chunk's operands.
+          constexpr int DSG = MODE == RQM_FP ? 0 : 1;
+          if (ok && leader) {
+            const uint32_t d_early = d_base + r * kRegionCols;
+            if constexpr (kind == CK_S && MODE == RQM_FP) {
+              constexpr uint32_t IDD = make_idesc_i8(kS, kS, 0, 0, 0, 0);
+              tc_fence_after();
+              umma_i8(d_early, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dqk16, 0, 128, 0), IDD, 0);
+              umma_i8(d_early, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(dqk16, 256, 128, 0), IDD, 1);
+            } else if constexpr (kind == CK_AV && MODE == RQM_FP) {
+              constexpr uint32_t IDD = make_idesc_i8(kS, NC, 0, 0, 0, 0);
+              tc_fence_after();
+              umma_i8(d_early, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dav16, 0, 128, 0), IDD, 0);
+            } else if constexpr (kind == CK_O) {
+              constexpr uint32_t IDD = make_idesc_i8(kS, E, DSG, DSG, 0, 0);
+              tc_fence_after();
+              umma_i8(d_early, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, C::OFF_WO + (P / 16) * E * 16, E * 16, 128), IDD, 0);
+              if constexpr (MODE == RQM_FP)
+                umma_i8(d_early, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(w16, C::OFF_WO + (P / 16 + 2) * E * 16, E * 16, 128), IDD, 1);
+            }
+          }
+          __syncwarp();
           if constexpr (c == 0) ok = ok && mbar_wait(b + BAR_X, ph, prm.abort_flag);
           if constexpr (c == C::C_S) ok = ok && mbar_wait(b + BAR_DEP + STG_Q, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_K, ph, prm.abort_flag);
           if constexpr (c == C::C_AV0) ok = ok && mbar_wait(b + BAR_DEP + STG_V, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_S, ph, prm.abort_flag);
@@ -869,8 +892,6 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
           tc_fence_after();
           ITA_TR(prm, warp, it, c, 2);
           const uint32_t d_tmem = d_base + r * kRegionCols;
-          // digit K steps: s8 digits against [1, 127, ...] (integer forms) or u8 digits against [1, 255, ...] (RQM_FP)
-          constexpr int DSG = MODE == RQM_FP ? 0 : 1;
           if (leader) {
             if constexpr (kind == CK_PROJ) {
               // projections: A = X [S rows, K = E] K-major; B = rows [col0, +NC) of [Wq | Wv | Wk]^T [3P rows, K = E + 32]
@@ -884,37 +905,29 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
               umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, wt + (E / 16) * C::PW * 16, C::PW * 16, 128),
                       IDD, 1);
             } else if constexpr (kind == CK_S) {
-              // logits: A = Q [S, K = P] K-major; B = K [S rows (keys), K = P] K-major; RQM_FP: + two offset steps
-              constexpr uint32_t ID = make_idesc_i8(kS, kS, 1, 1, 0, 0), IDD = make_idesc_i8(kS, kS, 0, 0, 0, 0);
+              // logits: A = Q [S, K = P] K-major; B = K [S rows (keys), K = P] K-major (RQM_FP: on top of the two offset steps)
+              constexpr uint32_t ID = make_idesc_i8(kS, kS, 1, 1, 0, 0);
 #pragma unroll
               for (int k = 0; k < P / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128), ID, k > 0);
-              if constexpr (MODE == RQM_FP) {
-                umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dqk16, 0, 128, 0), IDD, 1);
-                umma_i8(d_tmem, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(dqk16, 256, 128, 0), IDD, 1);
-              }
+                        make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128), ID, (k > 0 || MODE == RQM_FP) ? 1u : 0u);
             } else if constexpr (kind == CK_AV) {
               // context: A = Asm [S, K = S] u8 K-major (in the K buffer); B = columns [col0, +NC) of V [K = S rows, N = P]
-              // MN-major; RQM_FP: + one offset step
-              constexpr uint32_t ID = make_idesc_i8(kS, NC, 0, 1, 0, 1), IDD = make_idesc_i8(kS, NC, 0, 0, 0, 0);
+              // MN-major (RQM_FP: on top of the offset step)
+              constexpr uint32_t ID = make_idesc_i8(kS, NC, 0, 1, 0, 1);
 #pragma unroll
               for (int k = 0; k < kS / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(v16, (col0 / 16) * kS * 16 + k * 32 * 16, 128, kS * 16), ID, k > 0);
-              if constexpr (MODE == RQM_FP) umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dav16, 0, 128, 0), IDD, 1);
+                        make_smem_desc_rel(v16, (col0 / 16) * kS * 16 + k * 32 * 16, 128, kS * 16), ID, (k > 0 || MODE == RQM_FP) ? 1u : 0u);
             } else {
-              // output projection: A = O [S, K = P] K-major (in the Q buffer); B = Wo^T [E rows, K = P + 64]; one digit step
-              // (integer forms) or two (RQM_FP)
-              constexpr uint32_t ID = make_idesc_i8(kS, E, 1, 1, 0, 0), IDD = make_idesc_i8(kS, E, DSG, DSG, 0, 0);
+              // output projection: A = O [S, K = P] K-major (in the Q buffer); B = Wo^T [E rows, K = P + 64], on top of the
+              // digit steps issued above (one for the integer forms, two for RQM_FP)
+              constexpr uint32_t ID = make_idesc_i8(kS, E, 1, 1, 0, 0);
               constexpr uint32_t wo = C::OFF_WO;
 #pragma unroll
               for (int k = 0; k < P / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128), make_smem_desc_rel(w16, wo + k * 2 * E * 16, E * 16, 128),
-                        ID, k > 0);
-              umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, wo + (P / 16) * E * 16, E * 16, 128), IDD, 1);
-              if constexpr (MODE == RQM_FP)
-                umma_i8(d_tmem, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(w16, wo + (P / 16 + 2) * E * 16, E * 16, 128), IDD, 1);
+                        ID, 1);
             }
             umma_commit(b + BAR_FULL + r);
             if constexpr (c == C::C_TURN) mbar_arrive(b + BAR_TURN);

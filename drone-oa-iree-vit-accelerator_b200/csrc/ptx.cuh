@@ -64,7 +64,11 @@ __device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *a
       "{\n\t"
       ".reg .pred p, q;\n\t"
       ".reg .u32 n;\n\t"
-      "mov.u32 n, 0;\n"
+      "mov.u32 n, 0;\n\t"
+#ifndef ITA_NO_TESTWAIT
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"      // non-blocking probe: the common case is "already complete"
+      "@p bra ITA_DONE_%=;\n"
+#endif
       "ITA_WAIT_%=:\n\t"
 #ifdef ITA_WAIT_HINT_NS
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %4;\n\t"

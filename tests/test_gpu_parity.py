@@ -152,6 +152,39 @@ def test_edge_inputs(ita, R, RC):
     eng.close()
 
 
+@pytest.mark.parametrize("fp", ["1", "0"])
+def test_fused_requant_forms_at_accumulator_bounds(ita, R, RC, fp, monkeypatch):
+    """The production (non-dump) fused kernel in both requant forms -- FFMA.RM on offset accumulators (ITA_FUSED_FP=1,
+    default) and the integer IMAD forms (ITA_FUSED_FP=0) -- on inputs and weights that drive every accumulator to its
+    bound in both directions, plus ordinary frames: output bit-exact vs the oracle."""
+    monkeypatch.setenv("ITA_FUSED_FP", fp)
+    X = np.zeros((8, 128, 64), np.int8)
+    X[1] = 127
+    X[2] = -128
+    X[3, ::2] = 127
+    X[3, 1::2] = -128
+    X[4, :, ::2] = -128
+    X[4, :, 1::2] = 127
+    X[5:] = R.make_input(3, 128, 64, seed=9)
+    for case in range(4):
+        p = R.make_synthetic(128, 64, 192, 1, seed=6 + case, rand_add=(case % 2 == 1))
+        if case >= 1:
+            p.Wq[:] = 127 if case != 2 else -128
+            p.Wk[:] = -128
+            p.Wv[:, ::2] = 127
+            p.Wv[:, 1::2] = -128
+        if case == 3:
+            p.Wo[:] = 127
+        eng = _engine(ita, p)
+        if not eng.fused_supported:
+            pytest.skip(eng.fused_unsupported_reason())
+        ref = RC.mha(p, X)
+        y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
+        eng.sync_check()
+        _cmp(y, ref["Y"], f"fused forward at accumulator bounds, ITA_FUSED_FP={fp}, case {case}")
+        eng.close()
+
+
 # ----------------------------------------------------------------------------------------------------- golden fixtures
 def _fixture_params(R, q, pre, round_mode):
     from test_oracle import _block_params
