@@ -93,6 +93,14 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(load), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_threads() -> int:
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1, so the OpenMP default is not it)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_baseline(params, seconds: float = 10.0, native: bool = True):
     """Oracle port timed on this box's host cores; bounded sample (~`seconds` of CPU work)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -101,15 +109,16 @@ def cpu_baseline(params, seconds: float = 10.0, native: bool = True):
     lib = RC.load(native=native)
     chunk = 512
     X = R.make_input(chunk, params.S, params.E, seed=3)
-    lib.mha(params, X[:32], intermediates=False)          # warm-up (thread pool, page faults)
+    nt = host_threads()
+    lib.mha(params, X[:32], intermediates=False, nthreads=nt)          # warm-up (thread pool, page faults)
     n, t0 = 0, time.perf_counter()
     while True:
-        lib.mha(params, X, intermediates=False)
+        lib.mha(params, X, intermediates=False, nthreads=nt)
         n += chunk
         dt = time.perf_counter() - t0
         if dt >= seconds:
             break
-    return {"value": n / dt, "unit": "frames/s", "cores": lib.max_threads(), "kind": "port",
+    return {"value": n / dt, "unit": "frames/s", "cores": nt, "kind": "port",
             "sample": f"{n} frames of the same workload in {dt:.1f} s, oracle/ita_ref.c -O3 -march=native OpenMP over frames"}
 
 
@@ -125,11 +134,12 @@ def run_reference(args):
     p = R.make_synthetic(**CFG, seed=0)
     sample = 1024                                           # frames per step (bounded sample of the 4096-frame batch)
     X = R.make_input(sample, p.S, p.E, seed=3)
+    nt = host_threads()
     for _ in range(max(args.warmup, 1)):
-        lib.mha(p, X[:128], intermediates=False)
+        lib.mha(p, X[:128], intermediates=False, nthreads=nt)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        lib.mha(p, X, intermediates=False)
+        lib.mha(p, X, intermediates=False, nthreads=nt)
     dt = time.perf_counter() - t0
     fps = sample * args.steps / dt
     ops = R.ops_per_frame(**CFG)
@@ -138,7 +148,7 @@ def run_reference(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "s8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "sample_frames_per_step": sample},
             "int8_tops": fps * ops / 1e12,
-            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": lib.max_threads(), "kind": "port",
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": nt, "kind": "port",
                              "sample": f"{sample} frames/step x {args.steps} steps, oracle/ita_ref.c OpenMP, all host threads"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
