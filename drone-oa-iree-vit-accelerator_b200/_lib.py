@@ -48,6 +48,7 @@ SYMBOLS = {
     "ita_mha_fused_supported": (C.c_int, [C.c_void_p]),
     "ita_mha_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "ita_mha_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
+    "ita_mha_forward_host_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "ita_mha_forward_stages": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(MhaStages), C.c_void_p]),
     "ita_mha_forward_fused_debug": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(MhaStages), C.c_void_p]),
     "ita_mha_sync_check": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -195,6 +195,11 @@ void ita_mha_destroy(ita_mha_handle *h) {
   cudaFree(h->Wq); cudaFree(h->Wk); cudaFree(h->Wv); cudaFree(h->Wo); cudaFree(h->Wff); cudaFree(h->Wff2);
   cudaFree(h->Bq); cudaFree(h->Bk); cudaFree(h->Bv); cudaFree(h->Bo); cudaFree(h->Bff); cudaFree(h->Bff2);
   cudaFree(h->rq_dev); cudaFree(h->scratch); cudaFree(h->io_dev); cudaFree(h->abort_flag);
+  if (h->pipe_ready) {
+    for (int i = 0; i < 2; ++i) { cudaStreamDestroy(h->aux[i]); cudaEventDestroy(h->ev_done[i]); }
+    for (int i = 0; i < ita_mha_handle::kHostChunks; ++i) { cudaEventDestroy(h->ev_in[i]); cudaEventDestroy(h->ev_k[i]); }
+    cudaEventDestroy(h->ev_start);
+  }
   delete h;
 }
 
@@ -221,6 +226,13 @@ int ita_mha_forward(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64
 }
 
 int ita_mha_forward_host(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host, int64_t batch, int32_t path, void *cuda_stream) {
+  int rc = ita_mha_forward_host_async(h, x_host, y_host, batch, path, cuda_stream);
+  if (rc || batch == 0) return rc;
+  DeviceGuard guard(h->device);
+  return check_abort(h, (cudaStream_t)cuda_stream, "ita_mha_forward_host");
+}
+
+int ita_mha_forward_host_async(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host, int64_t batch, int32_t path, void *cuda_stream) {
   int rc = check_fwd_args("ita_mha_forward_host", h, x_host, y_host, batch);
   if (rc) return rc;
   if (batch == 0) return ITA_OK;
@@ -242,23 +254,26 @@ int ita_mha_forward_host(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host
   int8_t *xd = h->io_dev, *yd = h->io_dev + frame * (size_t)batch;
   // Pipeline the batch in chunks: the H2D copy of chunk i+1 and the D2H copy of chunk i-1 overlap the kernel of chunk i
   // when the caller's buffers are pinned (PCIe is full duplex); with pageable memory the copies serialise, still correct.
-  int64_t nchunk = batch >= 1024 ? 4 : 1;
+  // The copies are the cost (PCIe 5 x16: ~48 GB/s each way at once, the kernel is ~40x faster), so the chunks are small
+  // enough to keep the un-overlapped first H2D / last D2H short and large enough (>= 4 MB) to run at link speed.
+  int64_t nchunk = batch >= 4096 ? ita_mha_handle::kHostChunks : batch >= 1024 ? 4 : 1;
   if (path == ITA_PATH_AUTO) path = h->fused ? ITA_PATH_FUSED : ITA_PATH_STAGED;
   if (path == ITA_PATH_STAGED) nchunk = 1;   // the staged path shares one scratch area
   const int64_t per = (batch + nchunk - 1) / nchunk;
-  cudaStream_t aux[2] = {nullptr, nullptr};
-  cudaEvent_t ev_in[4], ev_k[4], ev_start, ev_done[2];
-  if (nchunk > 1) {
-    for (int i = 0; i < 2; ++i) ITA_CUDA_TRY(cudaStreamCreateWithFlags(&aux[i], cudaStreamNonBlocking));
-    for (int i = 0; i < 4; ++i) {
-      ITA_CUDA_TRY(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
-      ITA_CUDA_TRY(cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming));
+  if (nchunk > 1 && !h->pipe_ready) {
+    for (int i = 0; i < 2; ++i) ITA_CUDA_TRY(cudaStreamCreateWithFlags(&h->aux[i], cudaStreamNonBlocking));
+    for (int i = 0; i < ita_mha_handle::kHostChunks; ++i) {
+      ITA_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+      ITA_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_k[i], cudaEventDisableTiming));
     }
-    ITA_CUDA_TRY(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
-    for (int i = 0; i < 2; ++i) ITA_CUDA_TRY(cudaEventCreateWithFlags(&ev_done[i], cudaEventDisableTiming));
-    ITA_CUDA_TRY(cudaEventRecord(ev_start, s));
-    ITA_CUDA_TRY(cudaStreamWaitEvent(aux[0], ev_start, 0));
-    ITA_CUDA_TRY(cudaStreamWaitEvent(aux[1], ev_start, 0));
+    ITA_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_start, cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) ITA_CUDA_TRY(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+    h->pipe_ready = true;
+  }
+  if (nchunk > 1) {
+    ITA_CUDA_TRY(cudaEventRecord(h->ev_start, s));
+    ITA_CUDA_TRY(cudaStreamWaitEvent(h->aux[0], h->ev_start, 0));
+    ITA_CUDA_TRY(cudaStreamWaitEvent(h->aux[1], h->ev_start, 0));
   }
   rc = ITA_OK;
   for (int64_t c = 0; c < nchunk && !rc; ++c) {
@@ -270,33 +285,24 @@ int ita_mha_forward_host(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host
       if (!rc) ITA_CUDA_TRY(cudaMemcpyAsync(y_host, yd, frame * nb, cudaMemcpyDeviceToHost, s));
     } else {
       // aux[0]: H2D copies, s: kernels, aux[1]: D2H copies
-      ITA_CUDA_TRY(cudaMemcpyAsync(xd + frame * b0, x_host + frame * b0, frame * nb, cudaMemcpyHostToDevice, aux[0]));
-      ITA_CUDA_TRY(cudaEventRecord(ev_in[c], aux[0]));
-      ITA_CUDA_TRY(cudaStreamWaitEvent(s, ev_in[c], 0));
+      ITA_CUDA_TRY(cudaMemcpyAsync(xd + frame * b0, x_host + frame * b0, frame * nb, cudaMemcpyHostToDevice, h->aux[0]));
+      ITA_CUDA_TRY(cudaEventRecord(h->ev_in[c], h->aux[0]));
+      ITA_CUDA_TRY(cudaStreamWaitEvent(s, h->ev_in[c], 0));
       rc = forward_dev(h, xd + frame * b0, yd + frame * b0, nb, path, s);
       if (rc) break;
-      ITA_CUDA_TRY(cudaEventRecord(ev_k[c], s));
-      ITA_CUDA_TRY(cudaStreamWaitEvent(aux[1], ev_k[c], 0));
-      ITA_CUDA_TRY(cudaMemcpyAsync(y_host + frame * b0, yd + frame * b0, frame * nb, cudaMemcpyDeviceToHost, aux[1]));
+      ITA_CUDA_TRY(cudaEventRecord(h->ev_k[c], s));
+      ITA_CUDA_TRY(cudaStreamWaitEvent(h->aux[1], h->ev_k[c], 0));
+      ITA_CUDA_TRY(cudaMemcpyAsync(y_host + frame * b0, yd + frame * b0, frame * nb, cudaMemcpyDeviceToHost, h->aux[1]));
     }
   }
   if (nchunk > 1) {
     // join the helper streams back into `s`
-    cudaEventRecord(ev_done[0], aux[0]);
-    cudaEventRecord(ev_done[1], aux[1]);
-    cudaStreamWaitEvent(s, ev_done[0], 0);
-    cudaStreamWaitEvent(s, ev_done[1], 0);
+    cudaEventRecord(h->ev_done[0], h->aux[0]);
+    cudaEventRecord(h->ev_done[1], h->aux[1]);
+    cudaStreamWaitEvent(s, h->ev_done[0], 0);
+    cudaStreamWaitEvent(s, h->ev_done[1], 0);
   }
-  int rc2 = rc ? rc : check_abort(h, s, "ita_mha_forward_host");
-  if (nchunk > 1) {
-    cudaStreamSynchronize(aux[0]);
-    cudaStreamSynchronize(aux[1]);
-    for (int i = 0; i < 2; ++i) cudaStreamDestroy(aux[i]);
-    for (int i = 0; i < 4; ++i) { cudaEventDestroy(ev_in[i]); cudaEventDestroy(ev_k[i]); }
-    cudaEventDestroy(ev_start);
-    for (int i = 0; i < 2; ++i) cudaEventDestroy(ev_done[i]);
-  }
-  return rc2;
+  return rc;
 }
 
 int ita_mha_forward_stages(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64_t batch, const ita_mha_stages *stages,

@@ -68,6 +68,11 @@ struct ita_mha_handle {
   int8_t *io_dev = nullptr;             // device staging for ita_mha_forward_host
   size_t io_bytes = 0;
   int *abort_flag = nullptr;            // device int: set by a kernel whose bounded wait timed out
+  // ita_mha_forward_host pipeline (created on first use): aux[0] H2D copies, aux[1] D2H copies
+  static constexpr int kHostChunks = 8;
+  cudaStream_t aux[2] = {nullptr, nullptr};
+  cudaEvent_t ev_in[kHostChunks] = {}, ev_k[kHostChunks] = {}, ev_start = nullptr, ev_done[2] = {nullptr, nullptr};
+  bool pipe_ready = false;
   ita::FusedPlan *fused = nullptr;      // non-null when the fused tcgen05 kernel supports this handle
   std::string fused_reason;             // why not, otherwise
 };

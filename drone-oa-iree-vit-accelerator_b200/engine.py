@@ -132,8 +132,11 @@ class ITAEngine:
     def sync_check(self, stream: Optional[torch.cuda.Stream] = None) -> None:
         L.check(self.lib.ita_mha_sync_check(self._h, _stream_ptr(stream, self.device)), "ita_mha_sync_check")
 
-    def forward_host(self, x, out=None, path: int = L.PATH_AUTO, stream: Optional[torch.cuda.Stream] = None):
-        """x: int8 host ``np.ndarray`` or CPU ``torch.Tensor`` [B,S,E] (pinned memory makes the copies asynchronous)."""
+    def forward_host(self, x, out=None, path: int = L.PATH_AUTO, stream: Optional[torch.cuda.Stream] = None,
+                     sync: bool = True):
+        """x: int8 host ``np.ndarray`` or CPU ``torch.Tensor`` [B,S,E] (pinned memory makes the copies asynchronous).
+        ``sync=False`` returns as soon as the work is queued on ``stream``: the result is valid after ``sync_check(stream)``
+        (two engines on two streams then overlap one call's H2D copies with the other's D2H copies)."""
         is_np = isinstance(x, np.ndarray)
         xt = torch.from_numpy(x) if is_np else x
         if xt.is_cuda or xt.dtype != torch.int8 or not xt.is_contiguous():
@@ -142,9 +145,9 @@ class ITAEngine:
             raise ValueError(f"bad shape {tuple(xt.shape)}, expected [B,{self.S},{self.E}]")
         yt = torch.empty_like(xt) if out is None else (torch.from_numpy(out) if isinstance(out, np.ndarray) else out)
         with torch.cuda.device(self.device):
-            L.check(self.lib.ita_mha_forward_host(self._h, C.c_void_p(xt.data_ptr()), C.c_void_p(yt.data_ptr()),
-                                                  int(xt.shape[0]), path, _stream_ptr(stream, self.device)),
-                    "ita_mha_forward_host")
+            fn = self.lib.ita_mha_forward_host if sync else self.lib.ita_mha_forward_host_async
+            L.check(fn(self._h, C.c_void_p(xt.data_ptr()), C.c_void_p(yt.data_ptr()), int(xt.shape[0]), path,
+                       _stream_ptr(stream, self.device)), "ita_mha_forward_host")
         return yt.numpy() if is_np and out is None else (out if out is not None else yt)
 
     def _alloc_stages(self, B: int) -> Dict[str, torch.Tensor]:

@@ -19,7 +19,7 @@
  *       == what the IREE custom dispatch  void ITASelfAttention_workgroup(const T* input, T* output)  is meant to
  *       compute   samples/inference_udp_FPGA_custom_dispatch/plugin/ITA_dispatch.c:17-27 (decl ITA_spec.mlir:30-33):
  *       caller-owned in/out buffers of shape [B,S,E], no aliasing.
- *   ita_mha_forward_host
+ *   ita_mha_forward_host, ita_mha_forward_host_async
  *       the same call for a caller that owns HOST buffers (what main.cpp hands to iree_runtime_call_invoke,
  *       samples/inference_udp_FPGA_custom_dispatch/main.cpp:168-195): H2D copy, kernels, D2H copy, synchronous.
  *   ita_mha_forward_stages
@@ -116,6 +116,11 @@ ITA_API int ita_mha_forward(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_de
 /* same with HOST pointers (pinned or pageable): H2D, kernels, D2H, then synchronises the stream. */
 ITA_API int ita_mha_forward_host(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host, int64_t batch, int32_t path,
                          void *cuda_stream);
+/* same without the final synchronisation: every copy and kernel is ordered on `cuda_stream` (helper streams are joined
+ * back into it), y_host is valid once the stream has been synchronised (ita_mha_sync_check also reports device-side
+ * time-outs).  With two handles on two streams the H2D copies of one call overlap the D2H copies of the other. */
+ITA_API int ita_mha_forward_host_async(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host, int64_t batch, int32_t path,
+                               void *cuda_stream);
 /* staged kernels; writes every requested intermediate (DEVICE pointers) and y_dev (may be NULL). */
 ITA_API int ita_mha_forward_stages(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64_t batch,
                            const ita_mha_stages *stages, void *cuda_stream);

@@ -247,7 +247,8 @@ def test_ffn_fixture_on_gpu(ita, R, RC):
 def test_forward_host_and_chunked_pipeline(ita, R, RC):
     p = R.make_synthetic(128, 64, 192, 1, seed=6)
     eng = _engine(ita, p)
-    for B in (3, 1500):                      # 1500 >= 1024 takes the 4-chunk copy/compute pipeline
+    eng2 = _engine(ita, p)
+    for B in (3, 1500, 4100):                # >= 1024: 4-chunk copy/compute pipeline, >= 4096: 8 chunks (ragged last chunk)
         X = R.make_input(B, 128, 64, seed=B)
         want = RC.mha(p, X, intermediates=False)["Y"]
         y = eng.forward_host(X)
@@ -256,7 +257,16 @@ def test_forward_host_and_chunked_pipeline(ita, R, RC):
         yp = torch.empty_like(xp).pin_memory()
         eng.forward_host(xp, out=yp)
         _cmp(yp.numpy(), want, f"forward_host pinned B={B}")
+        # asynchronous entry: two handles on two streams, results valid after sync_check
+        outs = [torch.zeros_like(xp).pin_memory() for _ in range(2)]
+        streams = [torch.cuda.Stream(_dev()) for _ in range(2)]
+        for i, e in enumerate((eng, eng2)):
+            e.forward_host(xp, out=outs[i], stream=streams[i], sync=False)
+        for i, e in enumerate((eng, eng2)):
+            e.sync_check(streams[i])
+            _cmp(outs[i].numpy(), want, f"forward_host async handle {i} B={B}")
     eng.close()
+    eng2.close()
 
 
 def test_golden_facade_steps(ita, R):
