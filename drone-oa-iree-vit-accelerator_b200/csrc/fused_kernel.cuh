@@ -389,8 +389,8 @@ __device__ __forceinline__ void pair_sync(const PairCtx &pc) { named_bar_sync(pc
 // <= 127) and low saturation cannot matter (m >= -119: a saturated element has d > 8 either way); other rows (and
 // the other requant forms) take the general form with the explicit clamp.  The choice is made per warp; both warps of
 // a pair hold the same rows and therefore choose alike.
-template <int MODE, int ALT, bool DUMP, int HALF, class R>
-__device__ __forceinline__ void itamax_repo_half(uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
+template <int MODE, int ALT, bool DUMP, class R>
+__device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                  const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
   int2 *mine = pc.xch + HALF * kS + row, *other = pc.xch + (HALF ^ 1) * kS + row;
@@ -497,8 +497,8 @@ __device__ __forceinline__ void itamax_repo_half(uint32_t t, const FRq &rq, int8
 // The same ITAmax with the requantisation on the FMA pipe (RQM_FP).  TMEM holds bits = INIT + acc (monotone in acc), so
 // pass 1 takes the max of the raw patterns; z = rq_fp_bits(.) is a + 128 before saturation.  Fast rows (no logit
 // saturates high, m >= -119) get the distance d = m - a from one FFMA.RP per element; other rows clamp explicitly.
-template <bool DUMP, int HALF, class R>
-__device__ __forceinline__ void itamax_repo_half_fp(uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
+template <bool DUMP, class R>
+__device__ __forceinline__ void itamax_repo_half_fp(int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                     const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
   int2 *mine = pc.xch + HALF * kS + row, *other = pc.xch + (HALF ^ 1) * kS + row;
@@ -599,8 +599,8 @@ __device__ __forceinline__ void itamax_repo_half_fp(uint32_t t, const FRq &rq, i
 // Recalled golden-model streaming softmax (the stream16 variant): 16-column groups in
 // column order, running max m and denominator, eps = 1/32 with round-half-up; then out = inv >> rhu((m - a) / 32).
 // The row is walked in column order: HALF 1 continues from the state HALF 0 publishes.
-template <int MODE, bool DUMP, int HALF, class R>
-__device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
+template <int MODE, bool DUMP, class R>
+__device__ __forceinline__ void itamax_stream_half(int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                    const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
   auto biased = [&](uint32_t acc) -> uint32_t {   // sat8(requant) + 128 in [0, 255]
@@ -612,7 +612,7 @@ __device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, in
   };
   int2 *st0 = pc.xch + row, *st1 = pc.xch + kS + row;
   uint32_t m = 0, tot = 0;
-  if constexpr (HALF == 1) {
+  if (HALF == 1) {
     pair_sync(pc);                 // HALF 0 has published its running state
     m = (uint32_t)st0->x;
     tot = (uint32_t)st0->y;
@@ -637,7 +637,7 @@ __device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, in
                  }
                },
                NoRelease{});
-  if constexpr (HALF == 0) {
+  if (HALF == 0) {
     *st0 = make_int2((int)m, (int)tot);
     pair_sync(pc);
     pair_sync(pc);                 // HALF 1 has published the final state
@@ -681,8 +681,8 @@ __device__ __forceinline__ void itamax_stream_half(uint32_t t, const FRq &rq, in
 // One warpgroup (WG = 0: "A", 1: "B") of one slot: drains its sub-block of every chunk, in chunk order.  The chunk
 // schedule is unrolled at compile time: a lone warp issues one dependent instruction every ~5 cycles, so run-time chunk
 // bookkeeping (tried: a run-time loop over three code paths) costs more than the instruction-cache misses it saves.
-template <int E, int P, int MODE, int SOFTMAX, int ALT, bool DUMP, int WG>
-__device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const SlotCtx &sc, const PairCtx &pc, int quad, int lane, long long iters,
+template <int E, int P, int MODE, int SOFTMAX, int ALT, bool DUMP>
+__device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const SlotCtx &sc, const PairCtx &pc, int WG, int quad, int lane, long long iters,
                                               long long frame0, long long frame_stride) {
   using C = Cfg<E, P>;
   const int row = quad * 32 + lane;
@@ -695,7 +695,10 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
     const long long f = frame0 + it * frame_stride;
     static_for<0, C::NCH>([&](auto cc) {
       constexpr int c = decltype(cc)::value;
-      constexpr int kind = C::kind_of(c), SW = C::sub_w(c), stage = C::stage_of(c, WG), col0 = C::stage_col0(c, WG);
+      // both warpgroups run this one copy of the code (WG is a run-time value: a second, per-warpgroup copy of the unrolled
+      // schedule doubles the instruction footprint, and the kernel is instruction-fetch heavy -- see the ncu summary)
+      constexpr int kind = C::kind_of(c), SW = C::sub_w(c);
+      const int stage = WG ? C::stage_of(c, 1) : C::stage_of(c, 0), col0 = WG ? C::stage_col0(c, 1) : C::stage_col0(c, 0);
       if (!ok) return;
       const uint32_t r = n & 1u, use = n >> 1;
       ++n;
@@ -723,15 +726,15 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
           if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
         }
         if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && MODE == RQM_FP)
-          itamax_repo_half_fp<DUMP, WG>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+          itamax_repo_half_fp<DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
-          itamax_repo_half<MODE, ALT, DUMP, WG>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+          itamax_repo_half<MODE, ALT, DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else
-          itamax_stream_half<MODE, DUMP, WG>(taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+          itamax_stream_half<MODE, DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
       } else {
         int8_t *panel = stage == STG_Q ? q_buf : stage == STG_K ? k_buf : stage == STG_V ? v_buf : stage == STG_AV ? q_buf : nullptr;
         int8_t *g = nullptr;
-        if constexpr (stage == STG_O) {
+        if constexpr (kind == CK_O) {
           g = prm.y + (f * kS + row) * E + col0;
         } else if constexpr (DUMP) {
           int8_t *base = stage == STG_Q ? prm.dQ : stage == STG_K ? prm.dK : stage == STG_V ? prm.dV : prm.dO;
@@ -744,7 +747,7 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
                            },
                            release);
       }
-      if constexpr (stage != STG_O) {
+      if constexpr (kind != CK_O) {
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(sc.bars + BAR_DEP + stage);
@@ -955,10 +958,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
     const long long iters = iters_of(slot);
     if (iters > 0) {
       const long long frame0 = (long long)blockIdx.x * kSlots + slot;
-      if (wg == 0)
-        epilogue_loop<E, P, MODE, SOFTMAX, ALT, DUMP, 0>(prm, sc, pc, quad, lane, iters, frame0, frame_stride);
-      else
-        epilogue_loop<E, P, MODE, SOFTMAX, ALT, DUMP, 1>(prm, sc, pc, quad, lane, iters, frame0, frame_stride);
+      epilogue_loop<E, P, MODE, SOFTMAX, ALT, DUMP>(prm, sc, pc, wg, quad, lane, iters, frame0, frame_stride);
     }
   }
 
