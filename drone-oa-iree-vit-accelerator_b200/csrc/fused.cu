@@ -203,13 +203,39 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     if ((long long)ldexpf(fp[i].fc, 149) != Cc) fp_ok = false;
   }
   if (fp_ok) mode = RQM_FP;
+  // ---- RQM_TORCH_FP: the fp32 requant form on offset accumulators (no congruence: any INIT > |acc|max that fits the digits)
+  if (mode == RQM_TORCH) {
+    bool tfp_ok = true;
+    if (const char *e = getenv("ITA_FUSED_FP")) tfp_ok = atoi(e) != 0;
+    for (int i = 0; i < 6 && tfp_ok; ++i) {
+      const Rq &r = h->rq_host[stages[i] * h->H];
+      const long long bnd = (i == 4 && h->softmax_mode == ITA_SOFTMAX_REPO_GLOBAL) ? 255LL * 128 : bound[i];
+      const long long init = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
+      const long long bmx = (i < 3) ? bound[i] - (long long)E * 128 * 128 : (i == 5 ? bound[i] - (long long)P * 128 * 128 : 0);
+      const long long cap = (i == 3 || i == 5) ? cap64 : cap32;
+      const long long Cc = (long long)r.add + 128;
+      const float effs = ldexpf(r.eff, 23);
+      // (zp + 128 must be even: the final FFMA rounds t + zp + 128 to nearest-even, which equals rne(t) + zp + 128 on ties only
+      //  then; the reference's zero-points are all 0 -- symmetric quantisation, layers.py:10-21)
+      if (init + bnd >= (1LL << 24) || init + bmx > cap || Cc < 0 || (Cc & 1) || Cc >= (1LL << 23) || !(r.eff > 0.f) || !isfinite(effs) ||
+          ldexpf(effs, -23) != r.eff) {
+        tfp_ok = false;
+        break;
+      }
+      fp[i].init = (int32_t)init;
+      fp[i].fb = -ldexpf((float)init, -23);
+      fp[i].eff = effs;
+      fp[i].fc = ldexpf((float)Cc, -149);
+    }
+    if (tfp_ok) mode = RQM_TORCH_FP;
+  }
 
   FusedPlan *pl = new FusedPlan();
   pl->E = E; pl->P = P; pl->mode = mode; pl->softmax = h->softmax_mode; pl->smem_bytes = shape->smem_bytes;
   const int WA = P * (E + kBiasK), WO = E * (P + kBiasKO);
   const size_t wbytes = (size_t)3 * WA + WO + kConstBytes;
   std::vector<int8_t> host(wbytes, 0);
-  const bool fpm = (mode == RQM_FP);
+  const bool fpm = rqm_offset(mode);
   // stage index (Q K V QK AV O) of the three concatenated projections Q | V | K
   const int cat_stage[3] = {0, 2, 1};
   // [Wq | Wv | Wk]^T as ONE matrix [N = 3P rows, K = E + 32 cols] (the kernel's projection chunks are 128 consecutive rows of
@@ -262,7 +288,7 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     FRq f{};
     if (mode == RQM_TORCH) {
       f.add = r.add; f.eff = r.eff;
-    } else if (mode == RQM_FP) {
+    } else if (rqm_offset(mode)) {
       f = fp[i];
     } else if (mode == RQM_INT_HI) {
       f.multp = (int32_t)((long long)r.mult << (32 - r.shift));

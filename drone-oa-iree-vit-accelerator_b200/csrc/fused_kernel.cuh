@@ -70,7 +70,8 @@ constexpr int kBiasRadixU = 255;        // unsigned digits (RQM_FP)
 constexpr int kConstABytes = 8 * 64, kConstQKBytes = 8 * 64, kConstAVBytes = 8 * 32;
 constexpr int kConstBytes = kConstABytes + kConstQKBytes + kConstAVBytes;
 
-enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2, RQM_FP = 3 };
+enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2, RQM_FP = 3, RQM_TORCH_FP = 4 };
+__host__ __device__ constexpr bool rqm_offset(int mode) { return mode == RQM_FP || mode == RQM_TORCH_FP; }   // offset accumulators
 enum { STG_Q = 0, STG_K, STG_V, STG_S, STG_AV, STG_O };
 // per-slot mbarriers
 enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2 /* + region */, BAR_EMPTY = 4 /* + region */, BAR_DEP = 6 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */, BAR_TURN = 11 };
@@ -182,6 +183,11 @@ struct Cfg {
 //     elements turns that into s8.  (Checked exhaustively over +-4.3M accumulators x 59 parameter sets on B200:
 //     tools/fp_requant_check.cu.)
 // The ITAmax distance m - a + 1 = ceil((m + 129 - C) - bits*mult*2^-shift) is one FFMA.RP the same way.
+// RQM_TORCH_FP gives the reference's fp32 form  clamp(rne(fp32(acc) * eff) + zp)  the same treatment without the two
+// conversions (I2F, F2I run on the quarter-rate XU pipe): u = fma.rn(bits_f32, 2^126, -INIT*2^-23) = acc*2^-23 exactly,
+// t = u * (eff*2^23) rounds exactly like fp32(acc)*eff (power-of-two scalings are exact), and fma.rn(t, 2^-149, (zp+128)*2^-149)
+// rounds t to the nearest-even integer in the denormal ulp: its bit pattern is rne(t) + zp + 128 (for even zp, which keeps
+// the parity of ties; the reference's zero-points are 0).
 // (A first version preset the accumulators with tcgen05.st instead: a store needs distinct source registers, i.e. one
 //  register copy per column, which cost more than the FFMA saved.)
 // ---------------------------------------------------------------------------------------------------- requant forms
@@ -220,6 +226,17 @@ __device__ __forceinline__ uint32_t pack_u8x4(int y0, int y1, int y2, int y3) {
 }
 // RQM_FP: bit pattern of  y + 128  (sign bit set when negative) from the accumulator bit pattern
 __device__ __forceinline__ int rq_fp_bits(uint32_t v, const FRq &r) { return __float_as_int(__fmaf_rd(__uint_as_float(v), r.fb, r.fc)); }
+// RQM_TORCH_FP: the same for the fp32 requant form; fb = -INIT*2^-23, eff = eff*2^23, fc = (zp + 128)*2^-149
+__device__ __forceinline__ int rq_tfp_bits(uint32_t v, const FRq &r) {
+  const float u = __fmaf_rn(__uint_as_float(v), __uint_as_float(0x7E800000u) /* 2^126 */, r.fb);
+  const float t = __fmul_rn(u, r.eff);
+  return __float_as_int(__fmaf_rn(t, __uint_as_float(1u) /* 2^-149 */, r.fc));
+}
+template <int MODE>
+__device__ __forceinline__ int rq_off_bits(uint32_t v, const FRq &r) {
+  if constexpr (MODE == RQM_TORCH_FP) return rq_tfp_bits(v, r);
+  else return rq_fp_bits(v, r);
+}
 // X tile [kS rows x E bytes] -> panel layout: one 2-D TMA box (16 B x kS rows) per 16-byte column chunk
 template <int E>
 __device__ __forceinline__ void load_x_tile(void *dst, const CUtensorMap *map, long long frame, uint64_t *bar) {
@@ -346,9 +363,9 @@ __device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const F
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       int y[4];
-      if constexpr (MODE == RQM_FP) {
+      if constexpr (rqm_offset(MODE)) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) y[i] = rq_fp_bits(v[j + q * 4 + i], r);
+        for (int i = 0; i < 4; ++i) y[i] = rq_off_bits<MODE>(v[j + q * 4 + i], r);
         w[q] = pack_u8x4(y[0], y[1], y[2], y[3]) ^ 0x80808080u;
       } else {
 #pragma unroll
@@ -497,7 +514,7 @@ __device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq
 // The same ITAmax with the requantisation on the FMA pipe (RQM_FP).  TMEM holds bits = INIT + acc (monotone in acc), so
 // pass 1 takes the max of the raw patterns; z = rq_fp_bits(.) is a + 128 before saturation.  Fast rows (no logit
 // saturates high, m >= -119) get the distance d = m - a from one FFMA.RP per element; other rows clamp explicitly.
-template <bool DUMP, class R>
+template <int MODE, bool DUMP, class R>
 __device__ __forceinline__ void itamax_repo_half_fp(int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                     const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
@@ -512,11 +529,11 @@ __device__ __forceinline__ void itamax_repo_half_fp(int HALF, uint32_t t, const 
   mine->x = amax;
   pair_sync(pc);
   amax = max(amax, other->x);
-  const int zmax = rq_fp_bits((uint32_t)amax, rq);
+  const int zmax = rq_off_bits<MODE>((uint32_t)amax, rq);
   const int mp = min(max(zmax, 0), 255);          // m + 128
   bool fast = false;
 #ifndef ITA_FP_NOFAST
-  if constexpr (!DUMP) fast = __all_sync(0xffffffffu, zmax <= 255 && zmax >= 9);
+  if constexpr (!DUMP && MODE == RQM_FP) fast = __all_sync(0xffffffffu, zmax <= 255 && zmax >= 9);
 #endif
   uint32_t sum = 0;
   auto store16 = [&](int g, int j, const uint4 &ov) {
@@ -555,7 +572,7 @@ __device__ __forceinline__ void itamax_repo_half_fp(int HALF, uint32_t t, const 
                  },
                  release);
   } else {
-    auto dist = [&](uint32_t v) -> uint32_t { return (uint32_t)(mp - min(max(rq_fp_bits(v, rq), 0), 255)); };
+    auto dist = [&](uint32_t v) -> uint32_t { return (uint32_t)(mp - min(max(rq_off_bits<MODE>(v, rq), 0), 255)); };
     tmem_walk<2>(addr,
                  [&](auto, const uint32_t(&v)[32]) {
 #pragma unroll
@@ -604,8 +621,8 @@ __device__ __forceinline__ void itamax_stream_half(int HALF, uint32_t t, const F
                                                    const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
   auto biased = [&](uint32_t acc) -> uint32_t {   // sat8(requant) + 128 in [0, 255]
-    if constexpr (MODE == RQM_FP) {
-      return (uint32_t)min(max(rq_fp_bits(acc, rq), 0), 255);
+    if constexpr (rqm_offset(MODE)) {
+      return (uint32_t)min(max(rq_off_bits<MODE>(acc, rq), 0), 255);
     } else {
       return (uint32_t)(min(max(rq_apply<MODE, 0>((int)acc, rq, 0), -128), 127) + 128);
     }
@@ -725,8 +742,8 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
           if (prm.dA) gA = prm.dA + (f * kS + row) * kS;
           if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
         }
-        if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && MODE == RQM_FP)
-          itamax_repo_half_fp<DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+        if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && rqm_offset(MODE))
+          itamax_repo_half_fp<MODE, DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
           itamax_repo_half<MODE, ALT, DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else
@@ -866,15 +883,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
           ITA_TR(prm, warp, it, c, 1);
           // The digit K steps of the logits, the context and the output projection read only constants: they go first
           // (overwriting the region) and run while this thread still waits for the chunk's operands.
-          constexpr int DSG = MODE == RQM_FP ? 0 : 1;
+          constexpr int DSG = rqm_offset(MODE) ? 0 : 1;
           if (ok && leader) {
             const uint32_t d_early = d_base + r * kRegionCols;
-            if constexpr (kind == CK_S && MODE == RQM_FP) {
+            if constexpr (kind == CK_S && rqm_offset(MODE)) {
               constexpr uint32_t IDD = make_idesc_i8(kS, kS, 0, 0, 0, 0);
               tc_fence_after();
               umma_i8(d_early, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dqk16, 0, 128, 0), IDD, 0);
               umma_i8(d_early, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(dqk16, 256, 128, 0), IDD, 1);
-            } else if constexpr (kind == CK_AV && MODE == RQM_FP) {
+            } else if constexpr (kind == CK_AV && rqm_offset(MODE)) {
               constexpr uint32_t IDD = make_idesc_i8(kS, NC, 0, 0, 0, 0);
               tc_fence_after();
               umma_i8(d_early, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dav16, 0, 128, 0), IDD, 0);
@@ -882,7 +899,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
               constexpr uint32_t IDD = make_idesc_i8(kS, E, DSG, DSG, 0, 0);
               tc_fence_after();
               umma_i8(d_early, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, C::OFF_WO + (P / 16) * E * 16, E * 16, 128), IDD, 0);
-              if constexpr (MODE == RQM_FP)
+              if constexpr (rqm_offset(MODE))
                 umma_i8(d_early, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(w16, C::OFF_WO + (P / 16 + 2) * E * 16, E * 16, 128), IDD, 1);
             }
           }
@@ -913,7 +930,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
 #pragma unroll
               for (int k = 0; k < P / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128), ID, (k > 0 || MODE == RQM_FP) ? 1u : 0u);
+                        make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128), ID, (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
             } else if constexpr (kind == CK_AV) {
               // context: A = Asm [S, K = S] u8 K-major (in the K buffer); B = columns [col0, +NC) of V [K = S rows, N = P]
               // MN-major (RQM_FP: on top of the offset step)
@@ -921,7 +938,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
 #pragma unroll
               for (int k = 0; k < kS / 32; ++k)
                 umma_i8(d_tmem, make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(v16, (col0 / 16) * kS * 16 + k * 32 * 16, 128, kS * 16), ID, (k > 0 || MODE == RQM_FP) ? 1u : 0u);
+                        make_smem_desc_rel(v16, (col0 / 16) * kS * 16 + k * 32 * 16, 128, kS * 16), ID, (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
             } else {
               // output projection: A = O [S, K = P] K-major (in the Q buffer); B = Wo^T [E rows, K = P + 64], on top of the
               // digit steps issued above (one for the integer forms, two for RQM_FP)
@@ -992,6 +1009,7 @@ struct FusedShape {
   ITA_FUSED_ALT1(E, P, SM)                                                                                            \
   if (mode == RQM_INT_HI && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_HI, SM, 0, true> : k_ita_fused<E, P, RQM_INT_HI, SM, 0, false>;     \
   if (mode == RQM_INT_GEN && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_GEN, SM, 0, true> : k_ita_fused<E, P, RQM_INT_GEN, SM, 0, false>; \
+  if (mode == RQM_TORCH_FP && softmax == SM) return dump ? k_ita_fused<E, P, RQM_TORCH_FP, SM, 0, true> : k_ita_fused<E, P, RQM_TORCH_FP, SM, 0, false>; \
   if (mode == RQM_FP && softmax == SM) return dump ? k_ita_fused<E, P, RQM_FP, SM, 0, true> : k_ita_fused<E, P, RQM_FP, SM, 0, false>;           \
   if (mode == RQM_TORCH && softmax == SM) return dump ? k_ita_fused<E, P, RQM_TORCH, SM, 0, true> : k_ita_fused<E, P, RQM_TORCH, SM, 0, false>;
 

@@ -86,6 +86,31 @@ def test_fused_every_intermediate_vs_oracle(ita, R, EP, round_mode, softmax_mode
     eng.close()
 
 
+@pytest.mark.parametrize("EP", [(64, 192), (64, 64)])
+@pytest.mark.parametrize("fp", ["1", "0"])
+def test_fused_torch_form_zero_zero_points(ita, R, EP, fp, monkeypatch):
+    """fp32 requant form (round_mode torch_rne_f32) with the reference's zero zero-points: the fused kernel then runs it on
+    offset accumulators with three FFMAs per element (RQM_TORCH_FP; ITA_FUSED_FP=0: the I2F/FMUL/F2I form).  Every
+    intermediate (dump kernel) and the production kernel's output bit-exact vs the oracle, incl. saturating frames."""
+    monkeypatch.setenv("ITA_FUSED_FP", fp)
+    E, P = EP
+    p = R.make_synthetic(128, E, P, 1, seed=11, rand_add=False, round_mode=2, softmax_mode=0)
+    eng = _engine(ita, p)
+    if not eng.fused_supported:
+        pytest.skip(eng.fused_unsupported_reason())
+    X = R.make_input(9, 128, E, seed=12)
+    X[0] = 127
+    X[1] = -128
+    ref = R.mha_forward(p, X)
+    st = eng.forward_stages(torch.from_numpy(X).to(_dev()), fused_debug=True)
+    for k in STAGES:
+        _cmp(st[k], ref[k], f"fused torch form {k} E={E} P={P} ITA_FUSED_FP={fp}")
+    y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
+    eng.sync_check()
+    _cmp(y, ref["Y"], f"fused torch form forward Y ITA_FUSED_FP={fp}")
+    eng.close()
+
+
 @pytest.mark.parametrize("batch", [0, 1, 2, 3, 295, 296, 297, 1000])
 def test_fused_batch_sizes(ita, R, RC, batch):
     """Empty, single, odd, exactly one wave (2 x 148), one more, and multi-wave batches."""
