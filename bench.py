@@ -151,11 +151,30 @@ def run_reference(args):
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": nt, "kind": "port",
                              "sample": f"{sample} frames/step x {args.steps} steps, oracle/ita_ref.c OpenMP, all host threads"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
+_JSON_FD = None
+
+
+def emit(line: dict) -> None:
+    """The one JSON line, on the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    # stdout carries exactly one JSON line: everything else that libraries print there (NCCL's "NCCL version ..." banner
+    # at communicator creation, for one) is sent to stderr by pointing fd 1 at fd 2 for the duration of the run.
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
@@ -210,13 +229,13 @@ def main():
         torch.cuda.synchronize()
 
     # ---- device-resident throughput (value) + per-launch kernel time (roofline)
-    for i in range(W):
-        eng.forward(xs[i % NBUF], out=ys[i % NBUF], path=ita.PATH_FUSED)
-    eng.sync_check()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
         time.sleep(0.3)
+    for i in range(W):                                   # the W untimed warm-up steps, right before the timed region
+        eng.forward(xs[i % NBUF], out=ys[i % NBUF], path=ita.PATH_FUSED)
+    eng.sync_check()
     barrier()
     n0 = lib.ita_kernel_launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
@@ -320,7 +339,7 @@ def main():
             line["cpu_baseline"] = cpu_baseline(p, args.cpu_seconds)
         except Exception as e:   # the baseline is a reported figure, never the product path
             line["cpu_baseline"] = {"value": None, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
