@@ -114,7 +114,11 @@ struct Cfg {
   static constexpr int NAVC = (P + 127) / 128;                           // A.V chunks
   static constexpr int NCH = NPC + NAVC + 2;                             // + logits + output projection
   static constexpr int C_S = NPC, C_AV0 = NPC + 1, C_O = NPC + 1 + NAVC;
+#ifdef ITA_C_TURN
+  static constexpr int C_TURN = ITA_C_TURN;                              // tuning builds
+#else
   static constexpr int C_TURN = NPC >= 3 ? 2 : NPC - 1;                  // chunk whose issue lets the other slot start its frame
+#endif
   static constexpr int WP_BYTES = PW * (E + kBiasK);                     // [Wq | Wv | Wk]^T with bias digits
   static constexpr int WO_BYTES = E * (P + kBiasKO);                     // Wo^T with bias digits
   static constexpr int OFF_W = 0;
