@@ -223,6 +223,7 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
         break;
       }
       fp[i].init = (int32_t)init;
+      fp[i].negc = (int32_t)-Cc;
       fp[i].fb = -ldexpf((float)init, -23);
       fp[i].eff = effs;
       fp[i].fc = ldexpf((float)Cc, -149);
@@ -380,6 +381,10 @@ int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, cons
   prm.y = y;
   prm.batch = B;
   prm.abort_flag = h->abort_flag;
+  {
+    const char *e = getenv("ITA_FUSED_TORCH_FAST");      // tuning knob for RQM_TORCH_FP's fast ITAmax rows (default on)
+    prm.torch_fast = e ? atoi(e) : 1;
+  }
   for (int i = 0; i < 6; ++i) prm.rq[i] = pl->rq[i];
   if (dump) {
     prm.dQ = dump->Qp; prm.dK = dump->Kp; prm.dV = dump->Vp; prm.dA = dump->A; prm.dAsm = dump->Asm; prm.dO = dump->O;

@@ -103,6 +103,7 @@ struct FusedParams {
   int8_t *dQ, *dK, *dV, *dA;
   uint8_t *dAsm;
   int8_t *dO;
+  int torch_fast;            // RQM_TORCH_FP: take the one-FFMA-chain ITAmax distance on unsaturated rows (host knob)
   long long *trace;          // developer builds (-DITA_TRACE): [warp][iteration < 8][chunk][4] SM clock stamps of CTA 0
 };
 
@@ -519,7 +520,7 @@ __device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq
 // pass 1 takes the max of the raw patterns; z = rq_fp_bits(.) is a + 128 before saturation.  Fast rows (no logit
 // saturates high, m >= -119) get the distance d = m - a from one FFMA.RP per element; other rows clamp explicitly.
 template <int MODE, bool DUMP, class R>
-__device__ __forceinline__ void itamax_repo_half_fp(int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
+__device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                     const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
   int2 *mine = pc.xch + HALF * kS + row, *other = pc.xch + (HALF ^ 1) * kS + row;
@@ -537,7 +538,7 @@ __device__ __forceinline__ void itamax_repo_half_fp(int HALF, uint32_t t, const 
   const int mp = min(max(zmax, 0), 255);          // m + 128
   bool fast = false;
 #ifndef ITA_FP_NOFAST
-  if constexpr (!DUMP && MODE == RQM_FP) fast = __all_sync(0xffffffffu, zmax <= 255 && zmax >= 9);
+  if constexpr (!DUMP) fast = allow_fast && __all_sync(0xffffffffu, zmax <= 255 && zmax >= 9);
 #endif
   uint32_t sum = 0;
   auto store16 = [&](int g, int j, const uint4 &ov) {
@@ -546,18 +547,33 @@ __device__ __forceinline__ void itamax_repo_half_fp(int HALF, uint32_t t, const 
   if (fast) {
     // d + 1 = ceil((m + 129 - C) - bits*b) is >= 1 for every element of the row (an exact value in (-1, 0) would round to
     // -0.0, whose pattern is not 0), so the shifts below work on 2*256 and 2*inv8
-    const float c2 = __int_as_float(mp + 1 + rq.negc), nfb = -rq.fb;
-    auto dist = [&](uint32_t v) -> uint32_t { return (uint32_t)__float_as_int(__fmaf_ru(__uint_as_float(v), nfb, c2)); };
+    // (RQM_TORCH_FP: d + 1 = rne(-t) + (m + 129 - zp - 128), the last FFMA of the requant with -t and that constant, which
+    //  may be negative: sign-magnitude pattern -- and must be EVEN so that round-to-nearest-even keeps the parity of ties; an
+    //  odd constant is raised by one, the row then works with d + 2, still >= 1: never -0.0)
+    const int k2raw = mp + 1 + rq.negc;
+    const uint32_t odd = (MODE == RQM_TORCH_FP) ? (uint32_t)(k2raw & 1) : 0u;
+    const int k2 = k2raw + (int)odd;
+    const float c2 = __int_as_float(k2 >= 0 ? k2 : (int)(0x80000000u | (uint32_t)(-k2))), nfb = -rq.fb;
+    const uint32_t one = 512u << odd;
+    auto dist = [&](uint32_t v) -> uint32_t {
+      if constexpr (MODE == RQM_TORCH_FP) {
+        const float u = __fmaf_rn(__uint_as_float(v), __uint_as_float(0x7E800000u), rq.fb);
+        const float t = __fmul_rn(u, rq.eff);
+        return (uint32_t)__float_as_int(__fmaf_rn(-t, __uint_as_float(1u), c2));
+      } else {
+        return (uint32_t)__float_as_int(__fmaf_ru(__uint_as_float(v), nfb, c2));
+      }
+    };
     tmem_walk<2>(addr,
                  [&](auto, const uint32_t(&v)[32]) {
 #pragma unroll
-                   for (int i = 0; i < 32; ++i) sum += shr_clamp(512u, dist(v[i]));
+                   for (int i = 0; i < 32; ++i) sum += shr_clamp(one, dist(v[i]));
                  },
                  NoRelease{});
     mine->y = (int)sum;
     pair_sync(pc);
     sum += (uint32_t)other->y;
-    const uint32_t inv8 = (((255u * 65536u) / sum) >> 8) << 1;
+    const uint32_t inv8 = ((((255u * 65536u) / sum) >> 8) << 1) << odd;
     tmem_walk<2>(addr,
                  [&](auto gg, const uint32_t(&v)[32]) {
                    constexpr int g = decltype(gg)::value;
@@ -747,7 +763,7 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
           if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
         }
         if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && rqm_offset(MODE))
-          itamax_repo_half_fp<MODE, DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+          itamax_repo_half_fp<MODE, DUMP>(MODE == RQM_FP || prm.torch_fast != 0, WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
           itamax_repo_half<MODE, ALT, DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else
