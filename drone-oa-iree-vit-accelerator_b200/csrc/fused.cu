@@ -57,6 +57,7 @@ int make_x_tensor_map(CUtensorMap *map, const void *x, long long rows, int row_b
 
 struct FusedPlan {
   int E, P, mode, softmax, alt;
+  int torch_fast = 1;          // RQM_TORCH_FP: fast ITAmax rows (tuning knob ITA_FUSED_TORCH_FAST, read at handle creation)
   int smem_bytes;
   int8_t *wpanels = nullptr;   // device
   FRq rq[6];
@@ -233,6 +234,7 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
 
   FusedPlan *pl = new FusedPlan();
   pl->E = E; pl->P = P; pl->mode = mode; pl->softmax = h->softmax_mode; pl->smem_bytes = shape->smem_bytes;
+  if (const char *e = getenv("ITA_FUSED_TORCH_FAST")) pl->torch_fast = atoi(e);
   const int WA = P * (E + kBiasK), WO = E * (P + kBiasKO);
   const size_t wbytes = (size_t)3 * WA + WO + kConstBytes;
   std::vector<int8_t> host(wbytes, 0);
@@ -381,10 +383,7 @@ int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, cons
   prm.y = y;
   prm.batch = B;
   prm.abort_flag = h->abort_flag;
-  {
-    const char *e = getenv("ITA_FUSED_TORCH_FAST");      // tuning knob for RQM_TORCH_FP's fast ITAmax rows (default on)
-    prm.torch_fast = e ? atoi(e) : 1;
-  }
+  prm.torch_fast = pl->torch_fast;
   for (int i = 0; i < 6; ++i) prm.rq[i] = pl->rq[i];
   if (dump) {
     prm.dQ = dump->Qp; prm.dK = dump->Kp; prm.dV = dump->Vp; prm.dA = dump->A; prm.dAsm = dump->Asm; prm.dO = dump->O;
