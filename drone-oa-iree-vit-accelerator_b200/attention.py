@@ -19,7 +19,7 @@ import torch.nn as nn
 
 from . import _lib as L
 from .engine import ITAEngine, dequantize, quantize
-from .params import ITAQuantParams, calculate_hw_params
+from .params import ITAQuantParams, bias_to_int32, calculate_hw_params, linear_eff_f32
 
 
 class QuantizedLinearParams(nn.Module):
@@ -96,6 +96,14 @@ class ITASelfAttention(nn.Module):
             L.ST_V: s_x * self.v_proj.weight_scale / s_v, L.ST_QK: s_q * s_k / s_a, L.ST_AV: s_sm * s_v / s_o,
             L.ST_O: s_o * self.out_proj.weight_scale / s_out,
         }
+        # The fp32 requant scale as the reference backend forms it: quantized Linear (qnnpack) computes
+        # (f32(s_in) * f32(s_w)) / f32(s_out) in float32; the patched matmuls multiply by the double product cast to f32
+        # (tests/export_and_validation_W_B.py:139-142).  The two differ by an ulp now and then, which flips near-ties.
+        eff32 = {
+            L.ST_Q: linear_eff_f32(s_x, self.q_proj.weight_scale, s_q), L.ST_K: linear_eff_f32(s_x, self.k_proj.weight_scale, s_k),
+            L.ST_V: linear_eff_f32(s_x, self.v_proj.weight_scale, s_v), L.ST_QK: np.float32(effs[L.ST_QK]),
+            L.ST_AV: np.float32(effs[L.ST_AV]), L.ST_O: linear_eff_f32(s_o, self.out_proj.weight_scale, s_out),
+        }
         zps = {L.ST_Q: self.q_proj.zero_point, L.ST_K: self.k_proj.zero_point, L.ST_V: self.v_proj.zero_point,
                L.ST_QK: self.matmul1.zero_point, L.ST_AV: self.matmul2.zero_point, L.ST_O: self.out_proj.zero_point}
         mult = np.zeros((L.NUM_STAGES, H), np.int32)
@@ -105,14 +113,14 @@ class ITASelfAttention(nn.Module):
         for st, e in effs.items():
             mult[st], shift[st] = calculate_hw_params(e)
             add[st] = zps[st]
-            eff[st] = np.float32(e)
+            eff[st] = eff32[st]
 
         def split_w(lin):   # torch [H*hd, E] -> golden [H, E, hd]
             w = lin.weight_int8.cpu().numpy()
             return np.ascontiguousarray(w.reshape(H, hd, E).transpose(0, 2, 1))
 
         def bias_i32(lin, s_in):
-            return np.round(lin.bias.cpu().numpy().astype(np.float64) / (s_in * lin.weight_scale)).astype(np.int32)
+            return bias_to_int32(lin.bias.cpu().numpy(), s_in * lin.weight_scale)
 
         Wo = np.ascontiguousarray(self.out_proj.weight_int8.cpu().numpy().T.reshape(H, hd, E))   # [P_total,E] -> [H,hd,E]
         Bo = np.zeros((H, E), np.int32)

@@ -72,7 +72,14 @@ static int check_abort(ita_mha_handle *h, cudaStream_t s, const char *what) {
 }
 
 static int forward_dev(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, int path, cudaStream_t s) {
-  if (path == ITA_PATH_AUTO) path = h->fused ? ITA_PATH_FUSED : ITA_PATH_STAGED;
+  if (path == ITA_PATH_AUTO) {
+    path = h->fused ? ITA_PATH_FUSED : ITA_PATH_STAGED;
+    if (!h->fused && !h->warned_staged) {     // say it once: the staged kernels are the correctness path, not the fast one
+      h->warned_staged = true;
+      fprintf(stderr, "libita_b200: ITA_PATH_AUTO falls back to the staged (CUDA-core) kernels for S=%d E=%d P=%d H=%d: %s\n", h->S, h->E,
+              h->P, h->H, h->fused_reason.c_str());
+    }
+  }
   if (path == ITA_PATH_FUSED) return fused_forward(h, x, y, B, nullptr, s);
   if (path == ITA_PATH_STAGED) return staged_forward(h, x, y, B, nullptr, s);
   set_error("unknown path %d", path);
@@ -123,7 +130,8 @@ int ita_mha_create(const ita_mha_desc *d, ita_mha_handle **out) {
     set_error("ita_mha_create: F > 0 needs Wff/Wff2/Bff/Bff2");
     return ITA_ERR_INVALID;
   }
-  for (int i = 0; i < ITA_NUM_STAGES * d->H; ++i) {
+  // (mult, shift) are unused by the fp32 requant form: only eff[] matters there
+  for (int i = 0; i < ITA_NUM_STAGES * d->H && d->round_mode != ITA_ROUND_TORCH_RNE_F32; ++i) {
     if (d->shift[i] < 0 || d->shift[i] > 62 || d->mult[i] < 0 || d->mult[i] > 65535) {
       set_error("ita_mha_create: stage %d head %d: mult %d / shift %d out of range (0..65535 / 0..62)", i / d->H, i % d->H,
                 d->mult[i], d->shift[i]);
@@ -168,6 +176,7 @@ int ita_mha_create(const ita_mha_desc *d, ita_mha_handle **out) {
   for (int i = 0; i < ITA_NUM_STAGES * d->H; ++i) {
     Rq r;
     r.mult = d->mult[i]; r.shift = d->shift[i]; r.add = d->add[i]; r.mode = d->round_mode;
+    if (d->round_mode == ITA_ROUND_TORCH_RNE_F32 && (r.shift < 0 || r.shift > 62)) r.shift = 0;
     r.eff = d->eff ? d->eff[i] : 0.f;
     r.rnd = (d->round_mode == ITA_ROUND_HALF_UP && r.shift > 0) ? (1LL << (r.shift - 1)) : 0LL;
     h->rq_host[i] = r;

@@ -75,6 +75,7 @@ struct ita_mha_handle {
   bool pipe_ready = false;
   ita::FusedPlan *fused = nullptr;      // non-null when the fused tcgen05 kernel supports this handle
   std::string fused_reason;             // why not, otherwise
+  bool warned_staged = false;           // ITA_PATH_AUTO fallback notice printed
 };
 
 namespace ita {

@@ -15,8 +15,9 @@ namespace ita {
 extern const FusedShape fused_shape_64_192;
 static const FusedShape *const kShapes[] = {&fused_shape_64_192};
 #else
-extern const FusedShape fused_shape_64_192, fused_shape_64_64, fused_shape_64_128, fused_shape_128_64;
-static const FusedShape *const kShapes[] = {&fused_shape_64_192, &fused_shape_64_64, &fused_shape_64_128, &fused_shape_128_64};
+extern const FusedShape fused_shape_64_192, fused_shape_64_64, fused_shape_64_128, fused_shape_128_64, fused_shape_128_192, fused_shape_128_128;
+static const FusedShape *const kShapes[] = {&fused_shape_64_192,  &fused_shape_64_64,   &fused_shape_64_128,
+                                            &fused_shape_128_64, &fused_shape_128_192, &fused_shape_128_128};
 #endif
 
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -56,7 +57,7 @@ int make_x_tensor_map(CUtensorMap *map, const void *x, long long rows, int row_b
 }
 
 struct FusedPlan {
-  int E, P, mode, softmax, alt;
+  int E, P, mode, softmax, alt, slots, threads;
   int torch_fast = 1;          // RQM_TORCH_FP: fast ITAmax rows (tuning knob ITA_FUSED_TORCH_FAST, read at handle creation)
   int smem_bytes;
   int8_t *wpanels = nullptr;   // device
@@ -114,7 +115,7 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   const FusedShape *shape = nullptr;
   for (const FusedShape *s : kShapes)
     if (s->E == E && s->P == P) shape = s;
-  if (!shape) return no("fused kernel is instantiated for (E,P) in {(64,192),(64,64),(64,128),(128,64)}");
+  if (!shape) return no("fused kernel is instantiated for (E,P) in {(64,192),(64,64),(64,128),(128,64),(128,192),(128,128)}");
   int max_smem = 0;
   ITA_CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
   if (shape->smem_bytes > max_smem) return no("fused kernel needs more shared memory than the device offers");
@@ -143,22 +144,31 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
       }
   }
   // ---- worst-case accumulator magnitude per stage (bias included); must stay well inside s32
-  long long bound[6];
+  long long bound[6], bmaxs[6] = {0, 0, 0, 0, 0, 0};      // stage order Q K V QK AV O; bmaxs = largest |bias| of the stage
   {
+    // |x| <= 128, so a column's accumulator is bounded by 128 * sum_k |W[k][n]| + |b[n]| (far below the generic K * 2^14
+    // for real weights: the offsets of RQM_FP / RQM_TORCH_FP2 then fit one digit K step)
+    const int8_t *Wm[4] = {d->Wq, d->Wk, d->Wv, d->Wo};
     const int32_t *Bs[4] = {d->Bq, d->Bk, d->Bv, d->Bo};
-    const int n[4] = {P, P, P, E};
-    long long bmax[4] = {0, 0, 0, 0};
-    for (int t = 0; t < 4; ++t)
+    const int n[4] = {P, P, P, E}, Kd[4] = {E, E, E, P}, stage[4] = {0, 1, 2, 5};
+    for (int t = 0; t < 4; ++t) {
+      long long worst = 0, bm = 0;
       for (int j = 0; j < n[t]; ++j) {
-        long long b = Bs[t][j] < 0 ? -(long long)Bs[t][j] : Bs[t][j];
-        bmax[t] = b > bmax[t] ? b : bmax[t];
+        long long a = 0;
+        for (int k = 0; k < Kd[t]; ++k) {
+          const int w = Wm[t][(size_t)k * n[t] + j];
+          a += w < 0 ? -w : w;
+        }
+        const long long bb = Bs[t][j] < 0 ? -(long long)Bs[t][j] : Bs[t][j];
+        worst = std::max(worst, a * 128 + bb);
+        bm = std::max(bm, bb);
       }
-    bound[0] = (long long)E * 128 * 128 + bmax[0];
-    bound[1] = (long long)E * 128 * 128 + bmax[1];
-    bound[2] = (long long)E * 128 * 128 + bmax[2];
+      bound[stage[t]] = worst;
+      bmaxs[stage[t]] = bm;
+    }
     bound[3] = (long long)P * 128 * 128;
-    bound[4] = (long long)kS * 255 * 128;
-    bound[5] = (long long)P * 128 * 128 + bmax[3];
+    // A.V: with the repo ITAmax the probabilities of a row sum to <= 255 (sum_k (n_k*inv >> 16) <= 255*sum n/sum n)
+    bound[4] = (h->softmax_mode == ITA_SOFTMAX_REPO_GLOBAL) ? 255LL * 128 : (long long)kS * 255 * 128;
     for (int i = 0; i < 6; ++i)
       if (bound[i] >= (1LL << 30)) return no("bias magnitude too large for the fused kernel's s32 accumulate");
   }
@@ -170,8 +180,8 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   FRq fp[6] = {};
   bool fp_ok = (mode == RQM_INT_HI);
   if (const char *e = getenv("ITA_FUSED_FP")) fp_ok = fp_ok && atoi(e) != 0;    // tuning knob: 0 = keep the integer forms
-  const long long cap32 = kBiasRadixU - 1 + (long long)kBiasRadixU * 255 * (kBiasK - 1);
-  const long long cap64 = kBiasRadixU - 1 + (long long)kBiasRadixU * 255 * (kBiasKO - 1);
+  auto digit_cap = [](int ncols) { return (long long)kBiasRadixU - 1 + (long long)kBiasRadixU * 255 * (ncols - 1); };
+  const long long cap32 = digit_cap(kBiasK), cap64 = digit_cap(kBiasKO), cap96 = digit_cap(96);
   for (int i = 0; i < 6 && fp_ok; ++i) {
     const Rq &r = h->rq_host[stages[i] * h->H];
     if (r.mult <= 0 || r.shift < 1 || r.shift > 30) { fp_ok = false; break; }
@@ -180,8 +190,7 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     const int mb = r.shift - t;                                  // INIT is determined modulo 2^mb
     const long long rnd = r.rnd;
     if (mb < 0 || (rnd & ((1LL << t) - 1))) { fp_ok = false; break; }
-    // |acc|max; for A.V with the repo ITAmax the probabilities of a row sum to <= 255 (sum_k (n_k*inv >> 16) <= 255*sum n/sum n)
-    const long long bnd = (i == 4 && h->softmax_mode == ITA_SOFTMAX_REPO_GLOBAL) ? 255LL * 128 : bound[i];
+    const long long bnd = bound[i];
     const long long lo = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
     long long init = lo;
     if (mb > 0) {
@@ -194,9 +203,8 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     if ((init * r.mult - rnd) & ((1LL << r.shift) - 1)) { fp_ok = false; break; }
     const long long Cc = (rnd - init * r.mult) / (1LL << r.shift) + r.add + 128;
     // the stage's digit capacity: bias + offset (projections: one step; output projection, logits: two; context: one)
-    const long long bmx = (i < 3) ? bound[i] - (long long)E * 128 * 128 : (i == 5 ? bound[i] - (long long)P * 128 * 128 : 0);
     const long long cap = (i == 3 || i == 5) ? cap64 : cap32;
-    if (init + bnd >= (1LL << 24) || init + bmx > cap || Cc >= 0 || 257 - Cc >= (1LL << 24)) { fp_ok = false; break; }
+    if (init + bnd >= (1LL << 24) || init + bmaxs[i] > cap || Cc >= 0 || 257 - Cc >= (1LL << 24)) { fp_ok = false; break; }
     fp[i].init = (int32_t)init;
     fp[i].negc = (int32_t)-Cc;
     fp[i].fb = ldexpf((float)r.mult, -r.shift);
@@ -204,36 +212,50 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     if ((long long)ldexpf(fp[i].fc, 149) != Cc) fp_ok = false;
   }
   if (fp_ok) mode = RQM_FP;
-  // ---- RQM_TORCH_FP: the fp32 requant form on offset accumulators (no congruence: any INIT > |acc|max that fits the digits)
+  // ---- the fp32 requant form on offset accumulators.  RQM_TORCH_FP2 (two FFMAs per element) needs every stage's offset to
+  //      be a power of two that fits the stage's digit steps (one for the projections and A.V, two for the output projection,
+  //      three for Q.K^T); RQM_TORCH_FP (three) takes any INIT > |acc|max that fits (two steps for Q.K^T).
   if (mode == RQM_TORCH) {
-    bool tfp_ok = true;
-    if (const char *e = getenv("ITA_FUSED_FP")) tfp_ok = atoi(e) != 0;
-    for (int i = 0; i < 6 && tfp_ok; ++i) {
-      const Rq &r = h->rq_host[stages[i] * h->H];
-      const long long bnd = (i == 4 && h->softmax_mode == ITA_SOFTMAX_REPO_GLOBAL) ? 255LL * 128 : bound[i];
-      const long long init = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
-      const long long bmx = (i < 3) ? bound[i] - (long long)E * 128 * 128 : (i == 5 ? bound[i] - (long long)P * 128 * 128 : 0);
-      const long long cap = (i == 3 || i == 5) ? cap64 : cap32;
-      const long long Cc = (long long)r.add + 128;
-      const float effs = ldexpf(r.eff, 23);
-      // (zp + 128 must be even: the final FFMA rounds t + zp + 128 to nearest-even, which equals rne(t) + zp + 128 on ties only
-      //  then; the reference's zero-points are all 0 -- symmetric quantisation, layers.py:10-21)
-      if (init + bnd >= (1LL << 24) || init + bmx > cap || Cc < 0 || (Cc & 1) || Cc >= (1LL << 23) || !(r.eff > 0.f) || !isfinite(effs) ||
-          ldexpf(effs, -23) != r.eff) {
-        tfp_ok = false;
-        break;
+    bool allow = true;
+    if (const char *e = getenv("ITA_FUSED_FP")) allow = atoi(e) != 0;   // 0: conversion form; 1: three-FFMA form; default / 2: two-FFMA form when eligible
+    const bool want2 = !getenv("ITA_FUSED_FP") || atoi(getenv("ITA_FUSED_FP")) >= 2;
+    for (int form = want2 ? 2 : 1; form >= 1 && allow && mode == RQM_TORCH; --form) {
+      bool ok = true;
+      for (int i = 0; i < 6 && ok; ++i) {
+        const Rq &r = h->rq_host[stages[i] * h->H];
+        const long long bnd = bound[i];
+        long long init = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
+        if (form == 2)
+          while (init & (init - 1)) init += init & -init;          // round up to a power of two
+        const long long cap = (i == 3) ? (form == 2 ? cap96 : cap64) : (i == 5 ? cap64 : cap32);
+        const long long Cc = (long long)r.add + 128;
+        // (zp + 128 must be even: the final FFMA rounds t + zp + 128 to nearest-even, which equals rne(t) + zp + 128 on ties only
+        //  then; the reference's zero-points are all 0 -- symmetric quantisation, layers.py:10-21)
+        if (init + bnd >= (1LL << 24) || init + bmaxs[i] > cap || Cc < 0 || (Cc & 1) || Cc >= (1LL << 23) || !(r.eff > 0.f)) { ok = false; break; }
+        fp[i].init = (int32_t)init;
+        fp[i].negc = (int32_t)-Cc;
+        fp[i].fc = ldexpf((float)Cc, -149);
+        if (form == 2) {
+          // fb = eff * 2^85, eff = -INIT * eff * 2^-64 (exact: INIT is a power of two); both must be normal and exact scalings
+          const float b1 = ldexpf(r.eff, 85), c1 = -ldexpf(r.eff * (float)init, -64);
+          if (!isfinite(b1) || ldexpf(b1, -85) != r.eff || !(fabsf(c1) >= 1e-30f) || -ldexpf(c1, 64) != r.eff * (float)init ||
+              r.eff < 1e-9f || r.eff > 256.f) { ok = false; break; }
+          fp[i].fb = b1;
+          fp[i].eff = c1;
+        } else {
+          const float effs = ldexpf(r.eff, 23);
+          if (!isfinite(effs) || ldexpf(effs, -23) != r.eff) { ok = false; break; }
+          fp[i].fb = -ldexpf((float)init, -23);
+          fp[i].eff = effs;
+        }
       }
-      fp[i].init = (int32_t)init;
-      fp[i].negc = (int32_t)-Cc;
-      fp[i].fb = -ldexpf((float)init, -23);
-      fp[i].eff = effs;
-      fp[i].fc = ldexpf((float)Cc, -149);
+      if (ok) mode = form == 2 ? RQM_TORCH_FP2 : RQM_TORCH_FP;
     }
-    if (tfp_ok) mode = RQM_TORCH_FP;
   }
 
   FusedPlan *pl = new FusedPlan();
   pl->E = E; pl->P = P; pl->mode = mode; pl->softmax = h->softmax_mode; pl->smem_bytes = shape->smem_bytes;
+  pl->slots = shape->slots; pl->threads = shape->threads;
   if (const char *e = getenv("ITA_FUSED_TORCH_FAST")) pl->torch_fast = atoi(e);
   const int WA = P * (E + kBiasK), WO = E * (P + kBiasKO);
   const size_t wbytes = (size_t)3 * WA + WO + kConstBytes;
@@ -267,13 +289,14 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
             [&](int n, int k) { return k < P ? d->Wo[(size_t)k * E + n] : dig[(size_t)n * kBiasKO + (k - P)]; });
   // constant tiles: A operand of the digit steps [1, R, ..., R]; RQM_FP: the offset digits of Q.K^T and A.V
   {
-    int8_t row[64];
-    for (int k = 0; k < 64; ++k) row[k] = (int8_t)(uint8_t)(k == 0 ? 1 : (fpm ? kBiasRadixU : kBiasRadix));
+    int8_t row[96];
+    for (int k = 0; k < 96; ++k) row[k] = (int8_t)(uint8_t)(k == 0 ? 1 : (fpm ? kBiasRadixU : kBiasRadix));
     int8_t *ca = host.data() + (size_t)3 * WA + WO;
-    const_tile(ca, 64, row);
+    const_tile(ca, 96, row);
     if (fpm) {
-      digits_ok = offset_digits(fp[3].init, 64, row) && digits_ok;
-      const_tile(ca + kConstABytes, 64, row);
+      for (int k = 0; k < 96; ++k) row[k] = 0;
+      digits_ok = offset_digits(fp[3].init, 32 * rqm_qk_steps(mode), row) && digits_ok;
+      const_tile(ca + kConstABytes, 96, row);
       digits_ok = offset_digits(fp[4].init, 32, row) && digits_ok;
       const_tile(ca + kConstABytes + kConstQKBytes, 32, row);
     }
@@ -388,18 +411,18 @@ int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, cons
   if (dump) {
     prm.dQ = dump->Qp; prm.dK = dump->Kp; prm.dV = dump->Vp; prm.dA = dump->A; prm.dAsm = dump->Asm; prm.dO = dump->O;
   }
-  long long ctas = (B + kSlots - 1) / kSlots;
+  long long ctas = (B + pl->slots - 1) / pl->slots;
   if (ctas > h->sm_count) ctas = h->sm_count;
   KernelFn fn = dump ? pl->fn_dump : pl->fn;
 #ifdef ITA_TRACE
   static long long *trace_dev = nullptr;
-  const size_t trace_n = (size_t)(kThreads / 32) * (kTraceIters + 1) * 32 * 4;
+  const size_t trace_n = (size_t)(640 / 32) * (kTraceIters + 1) * 32 * 4;
   const char *trace_file = getenv("ITA_TRACE_FILE");
   if (!trace_dev) cudaMalloc(&trace_dev, trace_n * sizeof(long long));
   if (trace_file) cudaMemsetAsync(trace_dev, 0, trace_n * sizeof(long long), s);
   prm.trace = trace_dev;
 #endif
-  fn<<<(unsigned)ctas, kThreads, pl->smem_bytes, s>>>(map, prm);
+  fn<<<(unsigned)ctas, pl->threads, pl->smem_bytes, s>>>(map, prm);
   count_launch();
   ITA_CUDA_TRY(cudaGetLastError());
 #ifdef ITA_TRACE

@@ -51,11 +51,9 @@
 namespace ita {
 
 constexpr int kS = 128;                 // rows per tile = tcgen05 M
-constexpr int kSlots = 2;
+constexpr int kMaxSlots = 2;             // frames in flight per SM (Cfg<E,P>::SLOTS: 2 when the operand buffers fit twice, else 1)
 constexpr int kEpiWarpsPerSlot = 8;
-constexpr int kWarpMma = kSlots * kEpiWarpsPerSlot;     // + slot
-constexpr int kWarpLoad = kWarpMma + kSlots;
-constexpr int kThreads = (kWarpLoad + 1) * 32;
+constexpr int kSmemLimit = 232448;       // 227 KB: the per-block opt-in maximum of sm_100
 constexpr int kRegions = 2;             // accumulator ring per slot
 constexpr int kRegionCols = 128;
 constexpr int kTmemColsPerSlot = kRegions * kRegionCols;
@@ -65,13 +63,16 @@ constexpr int kBiasKO = 64;             // the output projection reserves two su
 constexpr int kBiasRadix = 127;         // signed digits (integer requant forms)
 constexpr int kBiasRadixU = 255;        // unsigned digits (RQM_FP)
 // Constant operand tiles, 8 rows each, read with SBO = 0 so that every 8-row group of the MMA operand aliases them:
-//   CA  [8 x 64]  A operand of the digit K steps: rows [1, R, R, ..., R]  (R = 127 s8 / 255 u8)
-//   DQK [8 x 64]  B operand of the two offset steps of Q.K^T (RQM_FP)     DAV [8 x 32]  B operand of the offset step of A.V
-constexpr int kConstABytes = 8 * 64, kConstQKBytes = 8 * 64, kConstAVBytes = 8 * 32;
+//   CA  [8 x 96]  A operand of the digit K steps: rows [1, R, R, ..., R]  (R = 127 s8 / 255 u8)
+//   DQK [8 x 96]  B operand of the offset steps of Q.K^T (two for RQM_FP / RQM_TORCH_FP, three for RQM_TORCH_FP2, whose
+//                 offset is a power of two)                               DAV [8 x 32]  B operand of the offset step of A.V
+constexpr int kConstABytes = 8 * 96, kConstQKBytes = 8 * 96, kConstAVBytes = 8 * 32;
 constexpr int kConstBytes = kConstABytes + kConstQKBytes + kConstAVBytes;
 
-enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2, RQM_FP = 3, RQM_TORCH_FP = 4 };
-__host__ __device__ constexpr bool rqm_offset(int mode) { return mode == RQM_FP || mode == RQM_TORCH_FP; }   // offset accumulators
+enum { RQM_INT_HI = 0, RQM_INT_GEN = 1, RQM_TORCH = 2, RQM_FP = 3, RQM_TORCH_FP = 4, RQM_TORCH_FP2 = 5 };
+__host__ __device__ constexpr bool rqm_offset(int mode) { return mode == RQM_FP || mode == RQM_TORCH_FP || mode == RQM_TORCH_FP2; }   // offset accumulators
+__host__ __device__ constexpr bool rqm_torch_fp(int mode) { return mode == RQM_TORCH_FP || mode == RQM_TORCH_FP2; }
+__host__ __device__ constexpr int rqm_qk_steps(int mode) { return mode == RQM_TORCH_FP2 ? 3 : 2; }   // offset digit K steps of Q.K^T
 enum { STG_Q = 0, STG_K, STG_V, STG_S, STG_AV, STG_O };
 // per-slot mbarriers
 enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2 /* + region */, BAR_EMPTY = 4 /* + region */, BAR_DEP = 6 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */, BAR_TURN = 11 };
@@ -136,12 +137,19 @@ struct Cfg {
   static constexpr int OFF_X = X_IN_KTAIL ? OFF_K + S * S : OFF_V + SP_BYTES;
   static constexpr int SLOT_BYTES = OFF_V + SP_BYTES + (X_IN_KTAIL ? 0 : X_BYTES);
   static constexpr int OFF_SLOT = ((WPANEL_BYTES + 127) / 128) * 128;
-  static constexpr int OFF_XCHG = OFF_SLOT + kSlots * SLOT_BYTES;        // softmax pair exchange: [slot][2 halves][S] int2
-  static constexpr int XCHG_BYTES = kSlots * 2 * S * 8;
+  // frames in flight per SM: two when weights + 2 x operand buffers fit the 227 KB, else one (E = 128 with P = 192)
+  static constexpr int smem_for(int slots) { return OFF_SLOT + slots * SLOT_BYTES + slots * 2 * S * 8 + 512; }
+  static constexpr int SLOTS = smem_for(kMaxSlots) <= kSmemLimit ? kMaxSlots : 1;
+  static constexpr int WARP_MMA = SLOTS * kEpiWarpsPerSlot;              // + slot: the MMA-issuing warp of the slot
+  static constexpr int WARP_LOAD = WARP_MMA + SLOTS;                     // TMA loader + TMEM allocator
+  static constexpr int THREADS = (WARP_LOAD + 1) * 32;
+  static constexpr int OFF_XCHG = OFF_SLOT + SLOTS * SLOT_BYTES;         // softmax pair exchange: [slot][2 halves][S] int2
+  static constexpr int XCHG_BYTES = SLOTS * 2 * S * 8;
   static constexpr int OFF_BAR = OFF_XCHG + XCHG_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 512;
+  static_assert(SMEM_BYTES <= kSmemLimit, "shape does not fit shared memory even with one frame in flight");
   static_assert(E % 64 == 0 && E <= 128 && P % 64 == 0, "E in {64, 128} (one output chunk), P a multiple of 64 (sub-block width)");
-  static_assert((1 + kSlots * kBarsPerSlot) * 8 + 8 <= 512, "barrier area");
+  static_assert((1 + kMaxSlots * kBarsPerSlot) * 8 + 8 <= 512, "barrier area");
   static_assert(WPANEL_BYTES % 16 == 0 && SLOT_BYTES % 128 == 0, "alignment");
   // chunk c of a frame -> kind, first column (in the concatenated Q|V|K space for projections), width (128 or 64)
   static constexpr int kind_of(int c) { return c < NPC ? CK_PROJ : c == C_S ? CK_S : c < C_O ? CK_AV : CK_O; }
@@ -237,10 +245,49 @@ __device__ __forceinline__ int rq_tfp_bits(uint32_t v, const FRq &r) {
   const float t = __fmul_rn(u, r.eff);
   return __float_as_int(__fmaf_rn(t, __uint_as_float(1u) /* 2^-149 */, r.fc));
 }
+// RQM_TORCH_FP2: the same in two FFMAs when the stage's offset INIT is a power of two (INIT*eff is then exactly
+// representable):  t' = fma.rn(bits_f32, eff*2^85, -INIT*eff*2^-64) = rn(acc*eff) * 2^-64  (one rounding of the exact product,
+// the same 24-bit rounding as fp32(acc)*eff -- everything stays in the normal range), then fma.rn(t', 2^-85, (zp+128)*2^-149)
+// rounds t + zp + 128 to nearest-even in the denormal ulp.  fb = eff*2^85, eff = -INIT*eff*2^-64, fc = (zp + 128)*2^-149.
+constexpr uint32_t kTwoM85 = 0x15000000u;        // 2^-85
+__device__ __forceinline__ int rq_tfp2_bits(uint32_t v, const FRq &r) {
+  const float t = __fmaf_rn(__uint_as_float(v), r.fb, r.eff);
+  return __float_as_int(__fmaf_rn(t, __uint_as_float(kTwoM85), r.fc));
+}
 template <int MODE>
 __device__ __forceinline__ int rq_off_bits(uint32_t v, const FRq &r) {
   if constexpr (MODE == RQM_TORCH_FP) return rq_tfp_bits(v, r);
+  else if constexpr (MODE == RQM_TORCH_FP2) return rq_tfp2_bits(v, r);
   else return rq_fp_bits(v, r);
+}
+// ---- packed f32x2 forms (FFMA2 / FMUL2, sm_100): two elements per issued instruction, same IEEE results (no .ftz: the
+//      denormal-range patterns are the point).  -DITA_NO_F32X2 keeps the scalar forms (A/B timing).
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk2(uint32_t lo, uint32_t hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi)); return r; }
+__device__ __forceinline__ u64 pk2f(float v) { return pk2(__float_as_uint(v), __float_as_uint(v)); }
+__device__ __forceinline__ void upk2(u64 v, int &lo, int &hi) { asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 ffma2_rn(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 ffma2_rm(u64 a, u64 b, u64 c) { u64 d; asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 ffma2_rp(u64 a, u64 b, u64 c) { u64 d; asm("fma.rp.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 fmul2_rn(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+template <int MODE>
+__device__ __forceinline__ void rq_off_bits2(uint32_t v0, uint32_t v1, const FRq &r, int &y0, int &y1) {
+#ifdef ITA_NO_F32X2
+  y0 = rq_off_bits<MODE>(v0, r);
+  y1 = rq_off_bits<MODE>(v1, r);
+#else
+  const u64 a = pk2(v0, v1);
+  u64 d;
+  if constexpr (MODE == RQM_TORCH_FP) {
+    const u64 u = ffma2_rn(a, pk2(0x7E800000u, 0x7E800000u), pk2f(r.fb));
+    d = ffma2_rn(fmul2_rn(u, pk2f(r.eff)), pk2(1u, 1u), pk2f(r.fc));
+  } else if constexpr (MODE == RQM_TORCH_FP2) {
+    d = ffma2_rn(ffma2_rn(a, pk2f(r.fb), pk2f(r.eff)), pk2(kTwoM85, kTwoM85), pk2f(r.fc));
+  } else {
+    d = ffma2_rm(a, pk2f(r.fb), pk2f(r.fc));
+  }
+  upk2(d, y0, y1);
+#endif
 }
 // X tile [kS rows x E bytes] -> panel layout: one 2-D TMA box (16 B x kS rows) per 16-byte column chunk
 template <int E>
@@ -369,8 +416,8 @@ __device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const F
     for (int q = 0; q < 4; ++q) {
       int y[4];
       if constexpr (rqm_offset(MODE)) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) y[i] = rq_off_bits<MODE>(v[j + q * 4 + i], r);
+        rq_off_bits2<MODE>(v[j + q * 4], v[j + q * 4 + 1], r, y[0], y[1]);
+        rq_off_bits2<MODE>(v[j + q * 4 + 2], v[j + q * 4 + 3], r, y[2], y[3]);
         w[q] = pack_u8x4(y[0], y[1], y[2], y[3]) ^ 0x80808080u;
       } else {
 #pragma unroll
@@ -551,23 +598,52 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
     //  may be negative: sign-magnitude pattern -- and must be EVEN so that round-to-nearest-even keeps the parity of ties; an
     //  odd constant is raised by one, the row then works with d + 2, still >= 1: never -0.0)
     const int k2raw = mp + 1 + rq.negc;
-    const uint32_t odd = (MODE == RQM_TORCH_FP) ? (uint32_t)(k2raw & 1) : 0u;
+    const uint32_t odd = rqm_torch_fp(MODE) ? (uint32_t)(k2raw & 1) : 0u;
     const int k2 = k2raw + (int)odd;
     const float c2 = __int_as_float(k2 >= 0 ? k2 : (int)(0x80000000u | (uint32_t)(-k2))), nfb = -rq.fb;
     const uint32_t one = 512u << odd;
-    auto dist = [&](uint32_t v) -> uint32_t {
+    // two distances per FFMA2
+    auto dist2 = [&](uint32_t v0, uint32_t v1, uint32_t &d0, uint32_t &d1) {
+#ifdef ITA_NO_F32X2
+      auto dist = [&](uint32_t v) -> uint32_t {
+        if constexpr (MODE == RQM_TORCH_FP) {
+          const float u = __fmaf_rn(__uint_as_float(v), __uint_as_float(0x7E800000u), rq.fb);
+          const float t = __fmul_rn(u, rq.eff);
+          return (uint32_t)__float_as_int(__fmaf_rn(-t, __uint_as_float(1u), c2));
+        } else if constexpr (MODE == RQM_TORCH_FP2) {
+          const float t = __fmaf_rn(__uint_as_float(v), rq.fb, rq.eff);
+          return (uint32_t)__float_as_int(__fmaf_rn(-t, __uint_as_float(kTwoM85), c2));
+        } else {
+          return (uint32_t)__float_as_int(__fmaf_ru(__uint_as_float(v), nfb, c2));
+        }
+      };
+      d0 = dist(v0);
+      d1 = dist(v1);
+#else
+      const u64 a = pk2(v0, v1);
+      u64 d;
       if constexpr (MODE == RQM_TORCH_FP) {
-        const float u = __fmaf_rn(__uint_as_float(v), __uint_as_float(0x7E800000u), rq.fb);
-        const float t = __fmul_rn(u, rq.eff);
-        return (uint32_t)__float_as_int(__fmaf_rn(-t, __uint_as_float(1u), c2));
+        const u64 u = ffma2_rn(a, pk2(0x7E800000u, 0x7E800000u), pk2f(rq.fb));
+        d = ffma2_rn(fmul2_rn(u, pk2f(rq.eff)), pk2(0x80000001u, 0x80000001u) /* -2^-149 */, pk2f(c2));
+      } else if constexpr (MODE == RQM_TORCH_FP2) {
+        d = ffma2_rn(ffma2_rn(a, pk2f(rq.fb), pk2f(rq.eff)), pk2(0x80000000u | kTwoM85, 0x80000000u | kTwoM85) /* -2^-85 */, pk2f(c2));
       } else {
-        return (uint32_t)__float_as_int(__fmaf_ru(__uint_as_float(v), nfb, c2));
+        d = ffma2_rp(a, pk2f(nfb), pk2f(c2));
       }
+      int i0, i1;
+      upk2(d, i0, i1);
+      d0 = (uint32_t)i0;
+      d1 = (uint32_t)i1;
+#endif
     };
     tmem_walk<2>(addr,
                  [&](auto, const uint32_t(&v)[32]) {
 #pragma unroll
-                   for (int i = 0; i < 32; ++i) sum += shr_clamp(one, dist(v[i]));
+                   for (int i = 0; i < 32; i += 2) {
+                     uint32_t d0, d1;
+                     dist2(v[i], v[i + 1], d0, d1);
+                     sum += shr_clamp(one, d0) + shr_clamp(one, d1);
+                   }
                  },
                  NoRelease{});
     mine->y = (int)sum;
@@ -582,10 +658,11 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
                      uint32_t w[4];
 #pragma unroll
                      for (int q = 0; q < 4; ++q) {
-                       int o[4];
-#pragma unroll
-                       for (int i = 0; i < 4; ++i) o[i] = (int)shr_clamp(inv8, dist(v[j + q * 4 + i]));
-                       w[q] = pack_u8x4(o[0], o[1], o[2], o[3]);
+                       uint32_t d[4];
+                       dist2(v[j + q * 4], v[j + q * 4 + 1], d[0], d[1]);
+                       dist2(v[j + q * 4 + 2], v[j + q * 4 + 3], d[2], d[3]);
+                       w[q] = pack_u8x4((int)shr_clamp(inv8, d[0]), (int)shr_clamp(inv8, d[1]), (int)shr_clamp(inv8, d[2]),
+                                        (int)shr_clamp(inv8, d[3]));
                      }
                      store16(g, j, make_uint4(w[0], w[1], w[2], w[3]));
                    }
@@ -763,7 +840,7 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
           if (prm.dAsm) gAsm = prm.dAsm + (f * kS + row) * kS;
         }
         if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL && rqm_offset(MODE))
-          itamax_repo_half_fp<MODE, DUMP>(MODE == RQM_FP || prm.torch_fast != 0, WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
+          itamax_repo_half_fp<MODE, DUMP>(!rqm_torch_fp(MODE) || prm.torch_fast != 0, WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else if constexpr (SOFTMAX == ITA_SOFTMAX_REPO_GLOBAL)
           itamax_repo_half<MODE, ALT, DUMP>(WG, taddr, prm.rq[3], k_buf, row, gA, gAsm, pc, release);
         else
@@ -796,8 +873,9 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
 
 // ---------------------------------------------------------------------------------------------------- the kernel
 template <int E, int P, int MODE, int SOFTMAX, int ALT, bool DUMP>
-__global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant__ CUtensorMap xmap, const FusedParams prm) {
+__global__ void __launch_bounds__((Cfg<E, P>::THREADS), 1) k_ita_fused(const __grid_constant__ CUtensorMap xmap, const FusedParams prm) {
   using C = Cfg<E, P>;
+  constexpr int kSlots = C::SLOTS, kWarpMma = C::WARP_MMA, kWarpLoad = C::WARP_LOAD;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + C::OFF_BAR);
   uint64_t *bar_w = bars;                          // weights + constant tile landed
@@ -893,7 +971,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
           // previous turn (slot 1: of the same iteration, slot 0: of the iteration before).  Left alone the slots fall into
           // lockstep (measured), where both sit in the same MMA-latency bubbles and the same epilogue bursts; out of phase
           // one slot's arithmetic fills the other's waits (+11 % measured).
-          if constexpr (c == 0) {
+          if constexpr (c == 0 && kSlots == 2) {
             uint64_t *other = slot_bars + (slot ^ 1) * kBarsPerSlot + BAR_TURN;
             if (slot == 1) ok = mbar_wait(other, ph, prm.abort_flag);
             else if (it > 0 && it - 1 < iters_of(1)) ok = mbar_wait(other, ph ^ 1u, prm.abort_flag);
@@ -911,6 +989,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_ita_fused(const __grid_constant
               tc_fence_after();
               umma_i8(d_early, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(dqk16, 0, 128, 0), IDD, 0);
               umma_i8(d_early, make_smem_desc_rel(ca16, 256, 128, 0), make_smem_desc_rel(dqk16, 256, 128, 0), IDD, 1);
+              if constexpr (rqm_qk_steps(MODE) == 3)
+                umma_i8(d_early, make_smem_desc_rel(ca16, 512, 128, 0), make_smem_desc_rel(dqk16, 512, 128, 0), IDD, 1);
             } else if constexpr (kind == CK_AV && rqm_offset(MODE)) {
               constexpr uint32_t IDD = make_idesc_i8(kS, NC, 0, 0, 0, 0);
               tc_fence_after();
@@ -1013,7 +1093,7 @@ typedef void (*KernelFn)(const CUtensorMap, const FusedParams);
 
 // One translation unit per (E, P) shape defines these (ITA_FUSED_DEFINE_SHAPE) so that the shapes compile in parallel.
 struct FusedShape {
-  int E, P, smem_bytes;
+  int E, P, smem_bytes, slots, threads;
   // mode: RQM_*; softmax: ITA_SOFTMAX_*; alt: INT_HI element form (0 / 1 / 2); dump: intermediates to global
   KernelFn (*pick)(int mode, int softmax, int alt, bool dump);
 };
@@ -1030,6 +1110,7 @@ struct FusedShape {
   if (mode == RQM_INT_HI && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_HI, SM, 0, true> : k_ita_fused<E, P, RQM_INT_HI, SM, 0, false>;     \
   if (mode == RQM_INT_GEN && softmax == SM) return dump ? k_ita_fused<E, P, RQM_INT_GEN, SM, 0, true> : k_ita_fused<E, P, RQM_INT_GEN, SM, 0, false>; \
   if (mode == RQM_TORCH_FP && softmax == SM) return dump ? k_ita_fused<E, P, RQM_TORCH_FP, SM, 0, true> : k_ita_fused<E, P, RQM_TORCH_FP, SM, 0, false>; \
+  if (mode == RQM_TORCH_FP2 && softmax == SM) return dump ? k_ita_fused<E, P, RQM_TORCH_FP2, SM, 0, true> : k_ita_fused<E, P, RQM_TORCH_FP2, SM, 0, false>; \
   if (mode == RQM_FP && softmax == SM) return dump ? k_ita_fused<E, P, RQM_FP, SM, 0, true> : k_ita_fused<E, P, RQM_FP, SM, 0, false>;           \
   if (mode == RQM_TORCH && softmax == SM) return dump ? k_ita_fused<E, P, RQM_TORCH, SM, 0, true> : k_ita_fused<E, P, RQM_TORCH, SM, 0, false>;
 
@@ -1039,6 +1120,6 @@ struct FusedShape {
     ITA_FUSED_PICK_SM(E, P, 1)                                                    \
     return nullptr;                                                               \
   }                                                                               \
-  extern const FusedShape fused_shape_##E##_##P = {E, P, Cfg<E, P>::SMEM_BYTES, pick_##E##_##P};
+  extern const FusedShape fused_shape_##E##_##P = {E, P, Cfg<E, P>::SMEM_BYTES, Cfg<E, P>::SLOTS, Cfg<E, P>::THREADS, pick_##E##_##P};
 
 }  // namespace ita

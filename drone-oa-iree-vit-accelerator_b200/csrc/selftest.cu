@@ -317,6 +317,38 @@ int microbench_run(int device, int kind, double *out, int n_out) {
     out[0] = best;
     if (n_out > 1) out[1] = sms;
     cudaFree(abort_flag);
+  } else if (kind == 3) {
+    // the same dense kind::i8 issue loop, back to back for out[0] seconds (input, default 2): the SUSTAINED int8 peak under
+    // the power cap -> out[0] = int8 TOP/s over the whole run, out[1] = seconds actually run
+    if (major != 10) {
+      set_error("ita_microbench: kind 3 needs an sm_100 device");
+      return ITA_ERR_UNSUPPORTED;
+    }
+    double want_s = out[0] > 0.05 && out[0] < 60 ? out[0] : 2.0;
+    int *abort_flag = nullptr;
+    ITA_CUDA_TRY(cudaMalloc(&abort_flag, sizeof(int)));
+    ITA_CUDA_TRY(cudaMemset(abort_flag, 0, sizeof(int)));
+    const int smem = (128 + 256) * 128;
+    ITA_CUDA_TRY(cudaFuncSetAttribute((const void *)k_umma_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int iters = 20000;                                   // ~5.5 ms per launch
+    const double ops1 = 2.0 * 128 * 256 * 128 * (double)iters * sms;
+    k_umma_peak<<<sms, 128, smem>>>(iters, abort_flag);        // warm-up
+    ITA_CUDA_TRY(cudaDeviceSynchronize());
+    double total_ms = 0, total_ops = 0;
+    while (total_ms * 1e-3 < want_s) {
+      ITA_CUDA_TRY(cudaEventRecord(e0));
+      for (int i = 0; i < 20; ++i) k_umma_peak<<<sms, 128, smem>>>(iters, abort_flag);
+      count_launch(20);
+      ITA_CUDA_TRY(cudaEventRecord(e1));
+      ITA_CUDA_TRY(cudaEventSynchronize(e1));
+      float ms = 0;
+      ITA_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+      total_ms += ms;
+      total_ops += 20 * ops1;
+    }
+    out[0] = total_ops / (total_ms * 1e-3) / 1e12;
+    if (n_out > 1) out[1] = total_ms * 1e-3;
+    cudaFree(abort_flag);
   } else if (kind == 1) {
     const size_t bytes = size_t(1) << 30;
     void *a = nullptr, *b = nullptr;

@@ -224,7 +224,9 @@ def selftest(device: int = 0) -> str:
     return rep
 
 
-def microbench(kind: int, device: int = 0):
+def microbench(kind: int, device: int = 0, arg: float = 0.0):
+    """``ita_microbench`` (roofline denominators).  ``arg`` is the input some kinds read from out[0] (kind 3: seconds)."""
     out = (C.c_double * 8)()
+    out[0] = float(arg)
     L.check(L.load().ita_microbench(device, kind, out, 8), "ita_microbench")
     return list(out)

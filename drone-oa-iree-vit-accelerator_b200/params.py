@@ -37,13 +37,26 @@ def calculate_hw_params(effective_scale: float):
     return mult, shift
 
 
+def linear_eff_f32(s_in: float, s_w: float, s_out: float) -> np.float32:
+    """Requantisation scale of a converted ``quantized.Linear`` exactly as the reference's backend (qnnpack) forms it:
+    ``(f32(s_in) * f32(s_w)) / f32(s_out)`` in float32 arithmetic.  (Computing it in double and casting differs by one
+    ulp now and then, which flips near-tie outputs: 1 of 16384 in the fc2 fixture.)"""
+    return np.float32(np.float32(np.float32(s_in) * np.float32(s_w)) / np.float32(s_out))
+
+
+def bias_to_int32(bias, s_acc: float) -> np.ndarray:
+    """``round(bias / s_acc)`` exactly as the reference evaluates it: a float32 bias array divided by a Python float stays
+    float32 in NumPy (the scalar is cast to float32), then round-half-even (``W_B.py:233-245``)."""
+    return np.round(np.asarray(bias, np.float32) / np.float32(s_acc)).astype(np.int32)
+
+
 def dequantize_bias_to_int32(layer_params: dict) -> np.ndarray:
     """``B_int32 = round(B_float / (S_input * S_weight))`` on the reference's captured-layer dictionary."""
     bias = layer_params["bias"]
     if bias is None:
         return np.zeros(layer_params["weight"]["q_value"].shape[0], dtype=np.int32)
     s_acc = layer_params["input"][0]["scale"] * layer_params["weight"]["scale"]
-    return np.round(np.asarray(bias) / s_acc).astype(np.int32)
+    return bias_to_int32(bias, s_acc)
 
 
 def translate_torch_scales_to_hw_params(attn_block: dict, ffn_block: dict, H: int) -> Dict[str, dict]:
@@ -54,7 +67,8 @@ def translate_torch_scales_to_hw_params(attn_block: dict, ffn_block: dict, H: in
             eff = (layer["input"][0]["scale"] * layer["weight"]["scale"]) / layer["output_scale"]
             m, s = calculate_hw_params(eff)
             n = 1 if key in ("fc1", "fc2") else H
-            hw[key] = {"mult": [m] * n, "shift": [s] * n, "add": [layer["output_zp"]] * n, "eff": [eff] * n}
+            e32 = float(linear_eff_f32(layer["input"][0]["scale"], layer["weight"]["scale"], layer["output_scale"]))
+            hw[key] = {"mult": [m] * n, "shift": [s] * n, "add": [layer["output_zp"]] * n, "eff": [e32] * n}
         elif layer.get("type") in ("MatMul_QK", "MatMul_AV"):
             so, zo = layer["output"]["scale"], layer["output"]["zp"]
             if key == "qk_matmul":
@@ -128,3 +142,44 @@ class ITAQuantParams:
         return ITAQuantParams(S=S, E=E, P=P, H=H, Wq=g("Wq"), Wk=g("Wk"), Wv=g("Wv"), Wo=g("Wo"), Bq=g("Bq"),
                               Bk=g("Bk"), Bv=g("Bv"), Bo=g("Bo"), mult=mult, shift=shift, add=add, eff=eff, F=F,
                               Wff=g("Wff"), Wff2=g("Wff2"), Bff=g("Bff"), Bff2=g("Bff2"), **modes)
+
+
+def params_from_captured_block(q, prefix: str = "b0_", round_mode: int = L.ROUND_TORCH_RNE_F32,
+                               softmax_mode: int = L.SOFTMAX_REPO_GLOBAL, with_ffn: bool = False) -> ITAQuantParams:
+    """Parameter set of one converted reference block from its flattened capture (the keys the reference's
+    ``PyTorchDataExtractor`` / ``organize_params_by_block`` produce, as stored in ``tests/golden/qat_*.npz``:
+    ``<prefix>{q,k,v,out}_proj_{w,sw,bias,sin,sout}``, ``qk_sout``, ``softmax_sout``, ``av_sout`` [, ``fc1_*``, ``fc2_*``]).
+
+    Follows the harness' recipe (``tests/export_and_validation_W_B.py:479-491,247-305``): ``W = weight.T[None]``,
+    ``B = round(bias / (s_in * s_w))``, ``eff = s_in1 * s_in2 / s_out`` -> ``calculate_hw_params``; the fp32 requant scales
+    are formed the way the backend forms them (``linear_eff_f32`` for Linear, double product cast to f32 for the matmuls).
+    H = 1 (every shipped model)."""
+    g = lambda k: q[prefix + k]
+    s = lambda k: float(q[prefix + k])
+    P, E = g("q_proj_w").shape
+    S = int(g("x").shape[-2]) if (prefix + "x") in q else 128
+    mult = np.zeros((L.NUM_STAGES, 1), np.int32)
+    shift = np.ones((L.NUM_STAGES, 1), np.int32)
+    add = np.zeros((L.NUM_STAGES, 1), np.int32)
+    eff = np.zeros((L.NUM_STAGES, 1), np.float32)
+    lin = {L.ST_Q: "q_proj", L.ST_K: "k_proj", L.ST_V: "v_proj", L.ST_O: "out_proj"}
+    if with_ffn:
+        lin.update({L.ST_FC1: "fc1", L.ST_FC2: "fc2"})
+    for st, n in lin.items():
+        mult[st, 0], shift[st, 0] = calculate_hw_params(s(n + "_sin") * s(n + "_sw") / s(n + "_sout"))
+        eff[st, 0] = linear_eff_f32(s(n + "_sin"), s(n + "_sw"), s(n + "_sout"))
+    for st, e in ((L.ST_QK, s("q_proj_sout") * s("k_proj_sout") / s("qk_sout")),
+                  (L.ST_AV, s("softmax_sout") * s("v_proj_sout") / s("av_sout"))):
+        mult[st, 0], shift[st, 0] = calculate_hw_params(e)
+        eff[st, 0] = np.float32(e)
+    T = lambda k: np.ascontiguousarray(np.asarray(g(k + "_w")).T[None]).astype(np.int8)
+    Bi = lambda k: bias_to_int32(g(k + "_bias"), s(k + "_sin") * s(k + "_sw"))[None]
+    kw = {}
+    if with_ffn:
+        F = int(g("fc1_w").shape[0])
+        # ReLU keeps the quantisation parameters (s_in == s_out): the golden model's relu requant is the identity
+        mult[L.ST_RELU, 0] = 0
+        kw = dict(F=F, Wff=T("fc1"), Wff2=T("fc2"), Bff=Bi("fc1"), Bff2=Bi("fc2"))
+    return ITAQuantParams(S=S, E=int(E), P=int(P), H=1, Wq=T("q_proj"), Wk=T("k_proj"), Wv=T("v_proj"), Wo=T("out_proj"),
+                          Bq=Bi("q_proj"), Bk=Bi("k_proj"), Bv=Bi("v_proj"), Bo=Bi("out_proj"), mult=mult, shift=shift, add=add,
+                          eff=eff, round_mode=round_mode, softmax_mode=softmax_mode, head_mode=L.HEADS_PYITA, **kw)

@@ -154,7 +154,9 @@ ITA_API int ita_selftest(int32_t device, char *report, int64_t report_len);
 
 /* Micro-benchmarks used by bench.py for the roofline denominators (results in `out`):
  *   kind 0: dense tcgen05 kind::i8 MMA issue rate -> out[0] = int8 TOP/s over the whole GPU
- *   kind 1: device-to-device copy                 -> out[0] = GB/s (read+write)                                     */
+ *   kind 1: device-to-device copy                 -> out[0] = GB/s (read+write)
+ *   kind 2: TMEM read bandwidth (developer)       -> out[0..7] = bytes per SM clock per SM
+ *   kind 3: kind 0 back to back for out[0] seconds (input; default 2) -> out[0] = sustained int8 TOP/s, out[1] = seconds  */
 ITA_API int ita_microbench(int32_t device, int32_t kind, double *out, int32_t n_out);
 
 #ifdef __cplusplus

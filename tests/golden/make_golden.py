@@ -177,8 +177,133 @@ def gen_qat_block(h, variant: str):
           {k: (v.shape if hasattr(v, 'shape') and getattr(v, 'ndim', 0) else v) for k, v in save.items() if k.startswith('b0_hw')})
 
 
+def gen_quantize():
+    """QuantStub at the operator's float boundary (reference models/ITA/QAT/layers.py:103): torch.quantize_per_tensor over
+    random floats and awkward scales (ties, saturation, denormal-ish scales)."""
+    rng = np.random.default_rng(7)
+    scales = np.array([0.5, 0.1, 0.05, 1.0 / 255.0, 0.0123456789, 3.3e-3, 7.77e-5, 1.9, 0.024999999, 2.0 ** -7], np.float64)
+    xs, qs = [], []
+    for s in scales:
+        x = (rng.standard_normal(4096) * s * 60).astype(np.float32)
+        x[:64] = (np.arange(-32, 32) + 0.5).astype(np.float32) * np.float32(s)          # exact ties
+        x[64:72] = np.array([1e30, -1e30, 127.5 * s, -128.5 * s, 127.49 * s, -128.51 * s, 0.0, -0.0], np.float32)
+        q = torch.quantize_per_tensor(torch.from_numpy(x), float(s), 0, torch.qint8).int_repr().numpy()
+        xs.append(x); qs.append(q)
+    np.savez_compressed(os.path.join(HERE, "quantize.npz"), scales=scales, x=np.stack(xs), q=np.stack(qs))
+    print("quantize.npz:", len(scales), "scales x 4096 floats")
+
+
+def gen_model(h):
+    """Full converted ITALSTMNetVIT_QAT (E=64, one layer) forward, every block boundary captured: tokenizer output,
+    attention in/out, residual + LayerNorm, FFN in/out, fusion, decoder, LSTM, head (reference
+    models/ITA_single_layer_upsample_shuffle/QAT/model.py:93-132).  Float parameters outside the int8 blocks come from
+    tests/golden/seeded.py (regenerated by name on the test side); the converted blocks' state-dict entries are saved with
+    torch.save exactly as a converted checkpoint holds them (tests/export_and_validation_W_B.py:387-392)."""
+    import seeded
+    torch.manual_seed(1)
+    torch.backends.quantized.engine = "qnnpack"
+    from models.ITA.QAT.layers import ita_symmetric_qconfig
+    from models.ITA_single_layer_upsample_shuffle.QAT.model import ITALSTMNetVIT_QAT
+    m = ITALSTMNetVIT_QAT(num_layers=1)
+    with torch.no_grad():
+        for name, prm in m.named_parameters():
+            if seeded.is_float_param(name):
+                prm.copy_(torch.from_numpy(seeded.float_param(name, prm.shape)))
+        for blk in list(m.attention_blocks) + list(m.ffn_blocks):
+            for lin in blk.modules():
+                if isinstance(lin, torch.nn.Linear):
+                    lin.weight.mul_(3.0)
+                    lin.bias.normal_(0, 0.3)
+    m.attention_blocks.qconfig = ita_symmetric_qconfig
+    m.ffn_blocks.qconfig = ita_symmetric_qconfig
+    mp = torch.ao.quantization.prepare_qat(m.train())
+    g = torch.Generator().manual_seed(5)
+    for _ in range(4):
+        mp([torch.rand(4, 1, 60, 90, generator=g), torch.rand(4, 1, generator=g), torch.rand(4, 4, generator=g), None])
+    mc = torch.ao.quantization.convert(mp.eval())
+    for block in mc.attention_blocks:
+        mm2 = block.matmul2
+        block.matmul2.matmul = (lambda s, z: (lambda a, b: h.custom_quantized_matmul(a, b, output_scale=s,
+                                                                                     output_zero_point=z)))(mm2.scale, mm2.zero_point)
+    B = 3
+    img = torch.rand(B, 1, 60, 90, generator=g)
+    vel = torch.rand(B, 1, generator=g) * 10
+    quat = torch.randn(B, 4, generator=g)
+    cap = {}
+
+    def hook(name):
+        def f(mod, inp, out):
+            o = out[0] if isinstance(out, tuple) else out
+            cap[name + "_in"] = inp[0].detach().clone() if isinstance(inp[0], torch.Tensor) else None
+            cap[name + "_out"] = o.detach().clone() if isinstance(o, torch.Tensor) else o
+        return f
+
+    hs = [mc.tokenizer.register_forward_hook(hook("tokenizer")), mc.attention_blocks[0].register_forward_hook(hook("attn")),
+          mc.norms1[0].register_forward_hook(hook("norm1")), mc.ffn_blocks[0].register_forward_hook(hook("ffn")),
+          mc.norms2[0].register_forward_hook(hook("norm2")), mc.down_sample.register_forward_hook(hook("down")),
+          mc.decoder.register_forward_hook(hook("decoder")), mc.nn_fc2.register_forward_hook(hook("fc"))]
+    with torch.no_grad():
+        out, (hn, cn) = mc([img.clone(), vel.clone(), quat.clone(), None])
+        for x in hs:
+            x.remove()
+        # second step carrying the LSTM state, as the deployed loop does (samples/.../main.cpp:217-224)
+        out2, (hn2, cn2) = mc([img.flip(0).clone(), vel.clone(), quat.clone(), (hn, cn)])
+    # per-block capture in the same key format as qat_block_*.npz
+    ext = h.PyTorchDataExtractor(mc)
+    flat = ext.extract_and_capture([img.clone(), vel.clone(), quat.clone(), None])
+    org = h.organize_params_by_block(flat)
+    at, ff = org["attention"][0], org["ffn"][0]
+    hw = h.translate_torch_scales_to_hw_params(at, ff, H=1)
+    save = {"img": img.numpy(), "vel": vel.numpy(), "quat": quat.numpy(), "out": out.numpy(), "hn": hn.numpy(), "cn": cn.numpy(),
+            "out2": out2.numpy(), "hn2": hn2.numpy(), "cn2": cn2.numpy()}
+    for k in ("tokenizer_out", "attn_in", "attn_out", "norm1_in", "norm1_out", "ffn_in", "ffn_out", "norm2_in", "norm2_out",
+              "down_in", "down_out", "decoder_out", "fc_out"):
+        save[k] = cap[k].numpy().astype(np.float32)
+    pre = "b0_"
+    save[pre + "x"] = at["q_proj"]["input"][0]["q_value"].astype(np.int8)
+    save[pre + "s_x"] = at["q_proj"]["input"][0]["scale"]
+    for nm in ("q_proj", "k_proj", "v_proj", "out_proj"):
+        save[pre + nm + "_w"] = at[nm]["weight"]["q_value"].astype(np.int8)
+        save[pre + nm + "_sw"] = at[nm]["weight"]["scale"]
+        save[pre + nm + "_bias"] = at[nm]["bias"].astype(np.float32)
+        save[pre + nm + "_sin"] = at[nm]["input"][0]["scale"]
+        save[pre + nm + "_sout"] = at[nm]["output_scale"]
+        save[pre + nm + "_out"] = at[nm]["output"]["q_value"].astype(np.int8)
+        save[pre + nm + "_bias_i32"] = h.dequantize_bias_to_int32(at[nm])
+    save[pre + "qk_out"] = at["qk_matmul"]["output"]["q_value"].astype(np.int8)
+    save[pre + "qk_sout"] = at["qk_matmul"]["output"]["scale"]
+    save[pre + "softmax_out"] = at["softmax"]["output"]["q_value"].astype(np.uint8)
+    save[pre + "softmax_sout"] = at["softmax"]["output"]["scale"]
+    save[pre + "av_out"] = at["av_matmul"]["output"]["q_value"].astype(np.int8)
+    save[pre + "av_sout"] = at["av_matmul"]["output"]["scale"]
+    for st in ("q_proj", "k_proj", "v_proj", "qk_matmul", "av_matmul", "out_proj"):
+        save[pre + "hw_" + st] = np.array([hw[st]["mult"][0], hw[st]["shift"][0], hw[st]["add"][0]], np.int64)
+    save[pre + "ffn_x"] = ff["fc1"]["input"][0]["q_value"].astype(np.int8)
+    for nm in ("fc1", "fc2"):
+        save[pre + nm + "_w"] = ff[nm]["weight"]["q_value"].astype(np.int8)
+        save[pre + nm + "_sw"] = ff[nm]["weight"]["scale"]
+        save[pre + nm + "_bias"] = ff[nm]["bias"].astype(np.float32)
+        save[pre + nm + "_sin"] = ff[nm]["input"][0]["scale"]
+        save[pre + nm + "_sout"] = ff[nm]["output_scale"]
+        save[pre + nm + "_out"] = ff[nm]["output"]["q_value"].astype(np.int8)
+        save[pre + nm + "_bias_i32"] = h.dequantize_bias_to_int32(ff[nm])
+        save[pre + "hw_" + nm] = np.array([hw[nm]["mult"][0], hw[nm]["shift"][0], hw[nm]["add"][0]], np.int64)
+    save[pre + "relu_out"] = ff["relu"]["output"]["q_value"].astype(np.int8)
+    np.savez_compressed(os.path.join(HERE, "qat_model_E64.npz"), **save)
+    # converted checkpoint entries of the int8 blocks (what torch.save(model.state_dict()) holds for them)
+    sd = {k: v for k, v in mc.state_dict().items() if not seeded.is_float_param(k)}
+    torch.save(sd, os.path.join(HERE, "qat_state_E64.pt"))
+    print("qat_model_E64.npz: out", out.numpy().round(4).tolist(), "| qat_state_E64.pt keys:", len(sd))
+    print("   state keys sample:", list(sd.keys())[:12])
+
+
 if __name__ == "__main__":
     h = _import_harness()
+    sys.path.insert(0, HERE)
+    if len(sys.argv) > 1 and sys.argv[1] == "--new":     # only the fixtures added in round 2 (the others stay as committed)
+        gen_quantize()
+        gen_model(h)
+        sys.exit(0)
     gen_itamax()
     gen_hw_params(h)
     gen_qat_block(h, "E64")

@@ -253,8 +253,22 @@ def test_itamax_fixture_on_gpu(ita, R):
         eng.close()
 
 
-def test_ffn_fixture_on_gpu(ita, R, RC):
-    q = np.load(os.path.join(GOLDEN, "qat_block_E64.npz"))
+@pytest.mark.parametrize("fixture", ["qat_block_E64.npz", "qat_block_E128.npz", "qat_model_E64.npz"])
+def test_ffn_fixture_on_gpu(ita, R, fixture):
+    """The converted reference FFN block (fc1 -> ReLU -> fc2, layers.py:61-75) through ``ita_ffn_forward``: the CUDA result
+    equals the reference's captured ``relu_out`` / ``fc2_out`` bit-exactly (torch_rne_f32, requant scale formed in float32
+    like the backend)."""
+    from test_oracle import _ffn_params
+    q = np.load(os.path.join(GOLDEN, fixture))
+    p = _ffn_params(R, q)
+    eng = _engine(ita, p)
+    f1, f2 = eng.ffn(torch.from_numpy(q["b0_ffn_x"]).to(_dev()), want_f1=True)
+    _cmp(f1, q["b0_relu_out"], f"ffn fixture {fixture} relu_out")
+    _cmp(f2, q["b0_fc2_out"], f"ffn fixture {fixture} fc2_out")
+    eng.close()
+
+
+def test_ffn_vs_oracle_all_roundings(ita, R, RC):
     p = R.make_synthetic(128, 64, 192, 1, seed=1, F=256, rand_add=True)
     for rm in (0, 1, 2):
         p.round_mode = rm
@@ -265,7 +279,36 @@ def test_ffn_fixture_on_gpu(ita, R, RC):
         _cmp(f1, ref["FF1"], f"ffn FF1 round={rm}")
         _cmp(f2, ref["FF2"], f"ffn FF2 round={rm}")
         eng.close()
-    assert "b0_fc1_w" in q.files
+
+
+def test_quantize_fixture_on_gpu(ita):
+    """QuantStub (layers.py:103): the CUDA quantiser equals torch.quantize_per_tensor on the reference-generated vectors
+    (random floats, exact ties, saturation, awkward scales); dequantise is scale * q exactly."""
+    g = np.load(os.path.join(GOLDEN, "quantize.npz"))
+    for s, x, q in zip(g["scales"], g["x"], g["q"]):
+        got = ita.quantize(torch.from_numpy(x).to(_dev()), float(s))
+        _cmp(got, q, f"quantize scale={float(s)}")
+        back = ita.dequantize(got, float(s)).cpu().numpy()
+        assert np.array_equal(back, q.astype(np.float32) * np.float32(s))
+
+
+def test_model_fixture_block_on_gpu(ita, R):
+    """The attention block inside the full converted model trace (qat_model_E64.npz): f32 in -> f32 out through the module
+    surface equals the reference's captured block output bit-exactly, every int8 stage included."""
+    from test_oracle import STAGE_FIX
+    q = np.load(os.path.join(GOLDEN, "qat_model_E64.npz"))
+    p = ita.params_from_captured_block(q, "b0_")
+    eng = ita.ITAEngine(p, _dev())
+    assert eng.fused_supported, eng.fused_unsupported_reason()
+    xq = ita.quantize(torch.from_numpy(q["attn_in"]).to(_dev()), float(q["b0_s_x"]))
+    _cmp(xq, q["b0_x"], "model fixture: quant stub")
+    for fused in (True, False):
+        st = eng.forward_stages(xq, fused_debug=fused)
+        for k, fk in STAGE_FIX.items():
+            _cmp(st[k], q["b0_" + fk], f"model fixture {'fused' if fused else 'staged'} {k}")
+    y = ita.dequantize(eng.forward(xq, path=ita.PATH_FUSED), float(q["b0_out_proj_sout"]))
+    assert np.array_equal(y.cpu().numpy(), q["attn_out"])
+    eng.close()
 
 
 # ----------------------------------------------------------------------------------------------------- host surfaces

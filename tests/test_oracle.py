@@ -48,11 +48,15 @@ def _block_params(R, q, pre, round_mode):
             R.ST_V: s("v_proj_sin") * s("v_proj_sw") / s("v_proj_sout"), R.ST_QK: s("q_proj_sout") * s("k_proj_sout") / s("qk_sout"),
             R.ST_AV: s("softmax_sout") * s("v_proj_sout") / s("av_sout"), R.ST_O: s("out_proj_sin") * s("out_proj_sw") / s("out_proj_sout")}
     names = {R.ST_Q: "q_proj", R.ST_K: "k_proj", R.ST_V: "v_proj", R.ST_QK: "qk_matmul", R.ST_AV: "av_matmul", R.ST_O: "out_proj"}
+    f32 = np.float32
+    lin32 = lambda n: f32(f32(f32(s(n + "_sin")) * f32(s(n + "_sw"))) / f32(s(n + "_sout")))   # qnnpack: float32 arithmetic
+    eff32 = {R.ST_Q: lin32("q_proj"), R.ST_K: lin32("k_proj"), R.ST_V: lin32("v_proj"), R.ST_O: lin32("out_proj"),
+             R.ST_QK: f32(effs[R.ST_QK]), R.ST_AV: f32(effs[R.ST_AV])}     # patched matmuls: double product cast to f32
     for st, e in effs.items():
         mult[st, 0], shift[st, 0], add[st, 0] = [int(v) for v in q[pre + "hw_" + names[st]]]
         if mult[st, 0] == 256:
             mult[st, 0], shift[st, 0] = 128, shift[st, 0] - 1
-        eff[st, 0] = np.float32(e)
+        eff[st, 0] = eff32[st]
         assert (int(mult[st, 0]), int(shift[st, 0])) == R.calculate_hw_params(e)
     T = lambda k: np.ascontiguousarray(q[pre + k + "_w"].T[None])
     B = lambda k: q[pre + k + "_bias_i32"][None].astype(np.int32)
@@ -65,12 +69,15 @@ STAGE_FIX = {"Qp": "q_proj_out", "Kp": "k_proj_out", "Vp": "v_proj_out", "A": "q
              "Y": "out_proj_out"}
 
 
-@pytest.mark.parametrize("variant,blocks", [("E64", 1), ("E128", 2)])
+def _fixture_file(variant):
+    return os.path.join(GOLDEN, f"qat_model_{variant[6:]}.npz" if variant.startswith("model_") else f"qat_block_{variant}.npz")
+
+
+@pytest.mark.parametrize("variant,blocks", [("E64", 1), ("E128", 2), ("model_E64", 1)])
 def test_converted_block_torch_rounding_bit_exact(R, RC, variant, blocks):
     """Whole converted ITASelfAttention_QAT block (qnnpack, matmul2 patched as W_B.py:408-423): in torch-rounding mode the
     oracle reproduces EVERY stage of the reference bit-exactly, stage by stage AND end to end."""
-    q = np.load(os.path.join(GOLDEN, f"qat_block_{variant}.npz"))
-    assert int(q["n_blocks"]) == blocks
+    q = np.load(_fixture_file(variant))
     for bi in range(blocks):
         pre = f"b{bi}_"
         p = _block_params(R, q, pre, R.ROUND_TORCH_RNE_F32)
@@ -100,28 +107,37 @@ def test_converted_block_golden_rounding_within_reference_tolerance(R, variant, 
             assert np.abs(out[k].astype(np.int32) - want).max() <= 1
 
 
-def test_ffn_fixture(R, RC):
-    """FFN block of the converted model: fc1 -> ReLU -> fc2 (reference models/ITA/QAT/layers.py:61-75)."""
-    q = np.load(os.path.join(GOLDEN, "qat_block_E64.npz"))
-    pre = "b0_"
+def _ffn_params(R, q, pre="b0_"):
+    """Oracle parameter set of the captured converted FFN block (fc1 -> ReLU -> fc2)."""
     x = q[pre + "ffn_x"]
     S, E = x.shape[1:]
     F = q[pre + "fc1_w"].shape[0]
     mult = np.zeros((R.NUM_STAGES, 1), np.int32); shift = np.ones((R.NUM_STAGES, 1), np.int32)
     add = np.zeros((R.NUM_STAGES, 1), np.int32); eff = np.zeros((R.NUM_STAGES, 1), np.float32)
     s = lambda k: float(q[pre + k])
-    eff[R.ST_FC1, 0] = np.float32(s("fc1_sin") * s("fc1_sw") / s("fc1_sout"))
-    eff[R.ST_FC2, 0] = np.float32(s("fc2_sin") * s("fc2_sw") / s("fc2_sout"))
+    f32 = np.float32          # the backend (qnnpack) forms the requant scale in float32 arithmetic
+    eff[R.ST_FC1, 0] = f32(f32(f32(s("fc1_sin")) * f32(s("fc1_sw"))) / f32(s("fc1_sout")))
+    eff[R.ST_FC2, 0] = f32(f32(f32(s("fc2_sin")) * f32(s("fc2_sw"))) / f32(s("fc2_sout")))
     z = np.zeros((1, E, 1), np.int8)
     p = R.ITAParams(S=S, E=E, P=1, H=1, Wq=z, Wk=z, Wv=z, Wo=np.zeros((1, 1, E), np.int8), Bq=np.zeros((1, 1), np.int32),
                     Bk=np.zeros((1, 1), np.int32), Bv=np.zeros((1, 1), np.int32), Bo=np.zeros((1, E), np.int32), mult=mult,
                     shift=shift, add=add, eff=eff, F=F, Wff=np.ascontiguousarray(q[pre + "fc1_w"].T[None]),
                     Wff2=np.ascontiguousarray(q[pre + "fc2_w"].T[None]), Bff=q[pre + "fc1_bias_i32"][None].astype(np.int32),
                     Bff2=q[pre + "fc2_bias_i32"][None].astype(np.int32), round_mode=R.ROUND_TORCH_RNE_F32)
+    p.mult[R.ST_RELU, 0] = 0          # quantised ReLU keeps the scale: no second requant
+    return p
+
+
+@pytest.mark.parametrize("fixture", ["qat_block_E64.npz", "qat_block_E128.npz", "qat_model_E64.npz"])
+def test_ffn_fixture(R, RC, fixture):
+    """FFN block of the converted model: fc1 -> ReLU -> fc2 (reference models/ITA/QAT/layers.py:61-75), bit-exact."""
+    q = np.load(os.path.join(GOLDEN, fixture))
+    pre = "b0_"
+    p = _ffn_params(R, q, pre)
+    x = q[pre + "ffn_x"]
     for out in (R.ffn_forward(p, x), RC.ffn(p, x)):
         assert np.array_equal(out["FF1"], q[pre + "relu_out"])
-        bad = int((out["FF2"] != q[pre + "fc2_out"]).sum())
-        assert bad <= 2, bad          # XNNPACK's fused requant differs from rne(f32(acc)*f32(eff)) on 1 of 16384 outputs
+        assert np.array_equal(out["FF2"], q[pre + "fc2_out"])   # bit-exact once eff is formed in float32 like the backend
 
 
 @pytest.mark.parametrize("dims", [(64, 64, 64, 1, 0), (128, 64, 192, 1, 256), (256, 128, 64, 4, 0), (32, 32, 32, 2, 64)])
@@ -202,3 +218,28 @@ def test_ops_per_frame(R):
     assert R.ops_per_frame(128, 64, 192, 1) == 25165824         # 25.17 Mop
     assert R.ops_per_frame(128, 64, 192, 1, 256) == 33554432    # 33.55 Mop with FFN
     assert R.ops_per_frame(256, 128, 64, 4) == 134217728        # 134.2 Mop
+
+
+def test_package_block_loader_matches_harness_recipe(R, ita):
+    """params_from_captured_block (product side) == the harness' recipe as restated for the oracle (_block_params)."""
+    for f, pre in (("qat_block_E64.npz", "b0_"), ("qat_block_E128.npz", "b0_"), ("qat_block_E128.npz", "b1_"), ("qat_model_E64.npz", "b0_")):
+        q = np.load(os.path.join(GOLDEN, f))
+        a, b = _block_params(R, q, pre, 2), ita.params_from_captured_block(q, pre, with_ffn=True)
+        for k in ("Wq", "Wk", "Wv", "Wo", "Bq", "Bk", "Bv", "Bo"):
+            assert np.array_equal(getattr(a, k), getattr(b, k)), (f, k)
+        for st in range(6):
+            assert (a.mult[st, 0], a.shift[st, 0], a.eff[st, 0]) == (b.mult[st, 0], b.shift[st, 0], b.eff[st, 0]), (f, st)
+        fp = _ffn_params(R, q, pre)
+        assert np.array_equal(fp.Wff, b.Wff) and np.array_equal(fp.Bff2, b.Bff2) and np.array_equal(fp.Bff, b.Bff)
+        assert fp.eff[R.ST_FC1, 0] == b.eff[R.ST_FC1, 0] and fp.eff[R.ST_FC2, 0] == b.eff[R.ST_FC2, 0]
+
+
+def test_quantize_fixture_definition():
+    """torch.quantize_per_tensor (the QuantStub of layers.py:103) == clamp(rne(x * f32(1/scale))) -- the form the CUDA quant
+    stub uses -- on the reference-generated vectors (ties, saturation, awkward scales)."""
+    g = np.load(os.path.join(GOLDEN, "quantize.npz"))
+    for s, x, q in zip(g["scales"], g["x"], g["q"]):
+        inv = np.float32(1.0) / np.float32(s)
+        with np.errstate(over="ignore", invalid="ignore"):
+            y = np.clip(np.rint(x * inv), -128, 127).astype(np.int8)
+        assert np.array_equal(y, q), float(s)

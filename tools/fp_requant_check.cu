@@ -33,6 +33,53 @@ __global__ void kdist(int init, float b, int negc, int mp, int mult, int shift, 
     if (want < 64 ? got != want : got < 64) atomicAdd(bad, 1ULL);
   }
 }
+// RQM_TORCH_FP2 (two packed FFMA2 per element pair, power-of-two offset) against the plain fp32 form
+//   want = sat_u8(rne(fp32(acc) * eff) + zp + 128)
+__global__ void ktorch2(int init, float eff, int zp, int lo, int hi, unsigned long long *bad) {
+  const float b1 = ldexpf(eff, 85), c1 = -ldexpf(eff * (float)init, -64), fc = __int_as_float(zp + 128);
+  unsigned long long B1, C1, M, FC;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(B1) : "f"(b1));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(C1) : "f"(c1));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(M) : "r"(0x15000000));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(FC) : "f"(fc));
+  for (long long acc = lo + 2 * (long long)(blockIdx.x * blockDim.x + threadIdx.x); acc + 1 <= hi; acc += 2LL * gridDim.x * blockDim.x) {
+    unsigned long long a, t, d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "r"(init + (int)acc), "r"(init + (int)acc + 1));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(t) : "l"(a), "l"(B1), "l"(C1));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(t), "l"(M), "l"(FC));
+    int r0, r1;
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(r0), "=r"(r1) : "l"(d));
+    for (int k = 0; k < 2; ++k) {
+      uint32_t packed;
+      asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(packed) : "r"(0), "r"(k ? r1 : r0), "r"(0));
+      int got = packed & 0xFF;
+      long long y = (long long)__float2int_rn(__fmul_rn(__int2float_rn((int)acc + k), eff)) + zp + 128;
+      int want = y < 0 ? 0 : (y > 255 ? 255 : (int)y);
+      if (got != want) atomicAdd(bad, 1ULL);
+    }
+  }
+}
+// RQM_FP with FFMA2.RM: same check as kcheck, two elements per instruction
+__global__ void kcheck2(int init, float b, float c, int mult, int shift, long long rnd, int add, int lo, int hi, unsigned long long *bad) {
+  unsigned long long Bp, Cp;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(Bp) : "f"(b));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(Cp) : "f"(c));
+  for (long long acc = lo + 2 * (long long)(blockIdx.x * blockDim.x + threadIdx.x); acc + 1 <= hi; acc += 2LL * gridDim.x * blockDim.x) {
+    unsigned long long a, d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "r"(init + (int)acc), "r"(init + (int)acc + 1));
+    asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(Bp), "l"(Cp));
+    int r0, r1;
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(r0), "=r"(r1) : "l"(d));
+    for (int k = 0; k < 2; ++k) {
+      uint32_t packed;
+      asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(packed) : "r"(0), "r"(k ? r1 : r0), "r"(0));
+      int got = packed & 0xFF;
+      long long y = (((acc + k) * mult + rnd) >> shift) + add + 128;
+      int want = y < 0 ? 0 : (y > 255 ? 255 : (int)y);
+      if (got != want) atomicAdd(bad, 1ULL);
+    }
+  }
+}
 static long long inv_odd(long long a, int bits) {  // inverse of odd a modulo 2^bits
   long long x = 1;
   for (int i = 0; i < 6; ++i) x = x * (2 - a * x);
@@ -66,6 +113,11 @@ int main() {
     cudaDeviceSynchronize();
     printf("mult %3d shift %2d add %2d rnd %lld init %lld C %lld: %llu mismatches\n", mult, shift, add, rnd, init, C, *bad);
     fails += *bad != 0;
+    *bad = 0;
+    kcheck2<<<296, 256>>>((int)init, b, c, mult, shift, rnd, add, -lim, lim, bad);
+    cudaDeviceSynchronize();
+    printf("   FFMA2.RM: %llu mismatches\n", *bad);
+    fails += *bad != 0;
     if (C < 0) {
       *bad = 0;
       kdist<<<296, 256>>>((int)init, b, (int)-C, 200, mult, shift, rnd, add, -lim, lim, bad);
@@ -73,6 +125,21 @@ int main() {
       printf("   dist: %llu mismatches\n", *bad);
       fails += *bad != 0;
     }
+  }
+  // fp32 requant form in two FFMA2 (power-of-two offsets 2^20 .. 2^22), random and awkward scales, zero-points 0 and 6
+  for (int trial = 0; trial < 24; ++trial) {
+    float eff = ldexpf(0.5f + (rand() % 8388608) / 16777216.0f, -(2 + rand() % 14));
+    if (trial == 0) eff = 0.0013240111f;
+    if (trial == 1) eff = ldexpf(1.f, -7);
+    if (trial == 2) eff = 0.99999994f * ldexpf(1.f, -5);
+    const int zp = (trial % 3 == 2) ? 6 : 0;
+    const int init = 1 << (20 + trial % 3);
+    const int lim = init - 2;
+    *bad = 0;
+    ktorch2<<<296, 256>>>(init, eff, zp, -lim, lim, bad);
+    cudaDeviceSynchronize();
+    printf("torch form, 2 x FFMA2: eff %.9g zp %d init 2^%d: %llu mismatches\n", eff, zp, 20 + trial % 3, *bad);
+    fails += *bad != 0;
   }
   printf(fails ? "FAILED\n" : "ALL EXACT\n");
   return fails != 0;

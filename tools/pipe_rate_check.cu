@@ -19,6 +19,14 @@ __global__ void k(int iters, long long *cyc, uint32_t *sink, uint32_t seed, floa
       if (OP == 4) a[i] = __float_as_uint(__fmaf_rd(__uint_as_float(a[i] | 0x3f800000u), 1.0001f, 0.5f));   // normal-range FFMA
       if (OP == 5) asm volatile("shr.u32 %0, %1, %0;" : "+r"(a[i]) : "r"(seed));
       if (OP == 6) asm volatile("prmt.b32 %0, %0, %1, 0x5140;" : "+r"(a[i]) : "r"(a[(i + 1) & 7]));
+      if (OP == 7 && (i & 1) == 0) {   // FFMA2.RM on denormal-range pairs: 4 instructions per 8 elements
+        unsigned long long v, bb, cc;
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(v) : "r"(a[i] & 0xFFFFFFu), "r"(a[i + 1] & 0xFFFFFFu));
+        asm volatile("mov.b64 %0, {%1, %1};" : "=l"(bb) : "f"(fb));
+        asm volatile("mov.b64 %0, {%1, %1};" : "=l"(cc) : "f"(fc));
+        asm volatile("fma.rm.f32x2 %0, %0, %1, %2;" : "+l"(v) : "l"(bb), "l"(cc));
+        asm volatile("mov.b64 {%0, %1}, %2;" : "=r"(a[i]), "=r"(a[i + 1]) : "l"(v));
+      }
     }
   }
   long long t1 = clock64();
@@ -31,9 +39,9 @@ __global__ void k(int iters, long long *cyc, uint32_t *sink, uint32_t seed, floa
 int main() {
   long long *cyc; uint32_t *sink;
   cudaMallocManaged(&cyc, 8); cudaMalloc(&sink, 4);
-  const char *names[] = {"cvt.pack.sat (I2IP)", "FFMA.RM denormal range (AND+FFMA)", "LOP3", "IMAD.HI(+IADD)", "FFMA.RM normal range (OR+FFMA)", "SHF", "PRMT"};
+  const char *names[] = {"cvt.pack.sat (I2IP)", "FFMA.RM denormal range (AND+FFMA)", "LOP3", "IMAD.HI(+IADD)", "FFMA.RM normal range (OR+FFMA)", "SHF", "PRMT", "FFMA2.RM denormal range (2 AND + FFMA2 per PAIR; per-element figure = this/1)"};
   const int iters = 20000, warps = 16;
-  for (int op = 0; op < 7; ++op) {
+  for (int op = 0; op < 8; ++op) {
     for (int rep = 0; rep < 2; ++rep) {
       if (op == 0) k<0><<<148, warps * 32>>>(iters, cyc, sink, 7, 1e-3f, 1e-40f);
       if (op == 1) k<1><<<148, warps * 32>>>(iters, cyc, sink, 7, 1e-3f, 1e-40f);
@@ -42,6 +50,7 @@ int main() {
       if (op == 4) k<4><<<148, warps * 32>>>(iters, cyc, sink, 7, 1e-3f, 1e-40f);
       if (op == 5) k<5><<<148, warps * 32>>>(iters, cyc, sink, 7, 1e-3f, 1e-40f);
       if (op == 6) k<6><<<148, warps * 32>>>(iters, cyc, sink, 7, 1e-3f, 1e-40f);
+      if (op == 7) k<7><<<148, warps * 32>>>(iters, cyc, sink, 7, 1e-3f, 1e-40f);
       cudaDeviceSynchronize();
     }
     double per = (double)cyc[0] / ((double)iters * 8 * (warps / 4));
