@@ -15,7 +15,7 @@ from ._lib import (HEADS_PYITA, HEADS_TORCH, PATH_AUTO, PATH_FUSED, PATH_STAGED,
                    ROUND_TORCH_RNE_F32, SOFTMAX_REPO_GLOBAL, SOFTMAX_STREAM16, ITAError)
 from .params import (ITAQuantParams, calculate_hw_params, dequantize_bias_to_int32, linear_eff_f32,
                      params_from_captured_block, translate_torch_scales_to_hw_params)
-from .engine import ITAEngine, dequantize, microbench, quantize, selftest
+from .engine import ITAEngine, dequantize, microbench, quantize, residual_layernorm, selftest
 from .attention import ITASelfAttention
 from .golden import Transformer
 from .sharding import all_shards, gather_frames, max_over_ranks, shard_range

@@ -38,6 +38,11 @@ class MhaStages(C.Structure):
                 ("O", C.c_void_p), ("Out", C.c_void_p)]
 
 
+class LayerParams(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("s_attn_in", "s_attn_out", "s_ffn_in", "s_ffn_out", "ln_eps")] + \
+               [(n, C.c_void_p) for n in ("ln1_w", "ln1_b", "ln2_w", "ln2_b")]
+
+
 # every symbol include/ita_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "ita_b200_abi_version": (C.c_int, []),
@@ -54,6 +59,11 @@ SYMBOLS = {
     "ita_mha_sync_check": (C.c_int, [C.c_void_p, C.c_void_p]),
     "ita_mha_step": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "ita_ffn_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "ita_ffn_forward_path": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
+    "ita_ffn_fused_supported": (C.c_int, [C.c_void_p]),
+    "ita_residual_layernorm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p,
+                                         C.c_void_p, C.c_float, C.c_int64, C.c_int32, C.c_void_p]),
+    "ita_encoder_layer_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "ita_quantize_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]),
     "ita_dequantize_s8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]),
     "ita_selftest": (C.c_int, [C.c_int32, C.c_char_p, C.c_int64]),

@@ -189,6 +189,7 @@ int ita_mha_create(const ita_mha_desc *d, ita_mha_handle **out) {
   }
   if (!rc && cudaMemset(h->abort_flag, 0, sizeof(int)) != cudaSuccess) rc = ITA_ERR_CUDA;
   if (!rc) rc = fused_plan_create(h, d);
+  if (!rc) rc = ffn_plan_create(h, d);
   if (rc) {
     ita_mha_destroy(h);
     return rc;
@@ -201,6 +202,8 @@ void ita_mha_destroy(ita_mha_handle *h) {
   if (!h) return;
   DeviceGuard guard(h->device);
   fused_plan_destroy(h);
+  ffn_plan_destroy(h);
+  cudaFree(h->layer_scratch);
   cudaFree(h->Wq); cudaFree(h->Wk); cudaFree(h->Wv); cudaFree(h->Wo); cudaFree(h->Wff); cudaFree(h->Wff2);
   cudaFree(h->Bq); cudaFree(h->Bk); cudaFree(h->Bv); cudaFree(h->Bo); cudaFree(h->Bff); cudaFree(h->Bff2);
   cudaFree(h->rq_dev); cudaFree(h->scratch); cudaFree(h->io_dev); cudaFree(h->abort_flag);
@@ -376,11 +379,50 @@ int ita_mha_step(ita_mha_handle *h, int32_t step, const void *in0, const void *i
   return staged_step(h, step, in0, in1, out, batch, (cudaStream_t)cuda_stream);
 }
 
-int ita_ffn_forward(ita_mha_handle *h, const int8_t *x_dev, int8_t *f1_dev, int8_t *f2_dev, int64_t batch, void *cuda_stream) {
+int ita_ffn_forward_path(ita_mha_handle *h, const int8_t *x_dev, int8_t *f1_dev, int8_t *f2_dev, int64_t batch, int32_t path,
+                         void *cuda_stream) {
   int rc = check_fwd_args("ita_ffn_forward", h, x_dev, f2_dev, batch);
   if (rc) return rc;
   DeviceGuard guard(h->device);
-  return staged_ffn(h, x_dev, f1_dev, f2_dev, batch, (cudaStream_t)cuda_stream);
+  if (path == ITA_PATH_AUTO) path = h->ffn ? ITA_PATH_FUSED : ITA_PATH_STAGED;
+  if (path == ITA_PATH_FUSED) return ffn_fused_forward(h, x_dev, f1_dev, f2_dev, batch, (cudaStream_t)cuda_stream);
+  if (path == ITA_PATH_STAGED) return staged_ffn(h, x_dev, f1_dev, f2_dev, batch, (cudaStream_t)cuda_stream);
+  set_error("unknown path %d", path);
+  return ITA_ERR_INVALID;
+}
+
+int ita_ffn_forward(ita_mha_handle *h, const int8_t *x_dev, int8_t *f1_dev, int8_t *f2_dev, int64_t batch, void *cuda_stream) {
+  return ita_ffn_forward_path(h, x_dev, f1_dev, f2_dev, batch, ITA_PATH_AUTO, cuda_stream);
+}
+
+int ita_ffn_fused_supported(const ita_mha_handle *h) {
+  if (!h) return 0;
+  if (h->ffn) return 1;
+  set_error("%s", h->ffn_reason.c_str());
+  return 0;
+}
+
+int ita_residual_layernorm(const float *x_dev, const int8_t *q_dev, float q_scale, const float *ln_w_dev, const float *ln_b_dev, float eps,
+                           float *y_dev, int8_t *yq_dev, float yq_scale, int64_t rows, int32_t E, void *cuda_stream) {
+  if (rows < 0 || (rows > 0 && (!x_dev || !q_dev || !ln_w_dev || !ln_b_dev || !y_dev))) {
+    set_error("ita_residual_layernorm: bad arguments");
+    return ITA_ERR_INVALID;
+  }
+  return launch_resid_ln(x_dev, q_dev, q_scale, ln_w_dev, ln_b_dev, eps, y_dev, yq_dev, yq_scale, rows, E, (cudaStream_t)cuda_stream);
+}
+
+int ita_encoder_layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x_dev, float *y_dev, int64_t batch,
+                              void *cuda_stream) {
+  if (!h || !lp || batch < 0 || (batch > 0 && (!x_dev || !y_dev)) || !lp->ln1_w || !lp->ln1_b || !lp->ln2_w || !lp->ln2_b) {
+    set_error("ita_encoder_layer_forward: null handle / parameter / buffer or negative batch");
+    return ITA_ERR_INVALID;
+  }
+  if (!(lp->s_attn_in > 0.f) || !(lp->s_ffn_in > 0.f)) {
+    set_error("ita_encoder_layer_forward: quantisation scales must be positive");
+    return ITA_ERR_INVALID;
+  }
+  DeviceGuard guard(h->device);
+  return layer_forward(h, lp, x_dev, y_dev, batch, (cudaStream_t)cuda_stream);
 }
 
 int ita_quantize_f32(const float *x_dev, int8_t *q_dev, int64_t n, float scale, void *cuda_stream) {

@@ -49,6 +49,7 @@ __device__ __forceinline__ int32_t requant_general(int32_t acc, const Rq &r) {
 
 // ---- handle ----------------------------------------------------------------------------------------------------------
 struct FusedPlan;   // fused.cu
+struct FfnPlan;     // ffn.cu
 
 }  // namespace ita
 
@@ -76,6 +77,10 @@ struct ita_mha_handle {
   ita::FusedPlan *fused = nullptr;      // non-null when the fused tcgen05 kernel supports this handle
   std::string fused_reason;             // why not, otherwise
   bool warned_staged = false;           // ITA_PATH_AUTO fallback notice printed
+  ita::FfnPlan *ffn = nullptr;          // non-null when the fused tcgen05 FFN kernel supports this handle
+  std::string ffn_reason;
+  int8_t *layer_scratch = nullptr;      // ita_encoder_layer_forward intermediates
+  size_t layer_scratch_bytes = 0;
 };
 
 namespace ita {
@@ -90,6 +95,14 @@ int launch_dequantize(const int8_t *q, float *y, int64_t n, float scale, cudaStr
 int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d);   // sets h->fused or h->fused_reason; returns ITA_OK unless CUDA fails
 void fused_plan_destroy(ita_mha_handle *h);
 int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, const ita_mha_stages *dump, cudaStream_t s);
+// ffn.cu
+int ffn_plan_create(ita_mha_handle *h, const ita_mha_desc *d);     // sets h->ffn or h->ffn_reason
+void ffn_plan_destroy(ita_mha_handle *h);
+int ffn_fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *f1, int8_t *f2, int64_t B, cudaStream_t s);
+// layer.cu
+int launch_resid_ln(const float *x, const int8_t *q, float sq, const float *gamma, const float *beta, float eps, float *y, int8_t *yq,
+                    float s_next, int64_t rows, int E, cudaStream_t s);
+int layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x, float *y, int64_t B, cudaStream_t s);
 // selftest.cu
 int selftest_run(int device, std::string &report);
 int microbench_run(int device, int kind, double *out, int n_out);

@@ -73,7 +73,7 @@ static void to_panels(int8_t *dst, int R, int Ccols, F at) {
 }
 
 // int32 bias -> kBiasK signed digits g with  b = g[0] + kBiasRadix * (g[1] + ... + g[kBiasK-1]),  every g in [-127, 127]
-static bool bias_digits(int32_t b, int8_t *g) {
+bool bias_digits(int32_t b, int8_t *g) {
   long long q = (b >= 0 ? (b + kBiasRadix / 2) : -((-(long long)b + kBiasRadix / 2))) / kBiasRadix;   // round to nearest
   long long rem = (long long)b - q * kBiasRadix;                                                      // |rem| <= 63
   g[0] = (int8_t)rem;
@@ -86,7 +86,7 @@ static bool bias_digits(int32_t b, int8_t *g) {
 }
 
 // non-negative value -> n unsigned digits g with  v = g[0] + kBiasRadixU * (g[1] + ... + g[n-1]),  every g in [0, 255]
-static bool offset_digits(long long v, int n, int8_t *g) {
+bool offset_digits(long long v, int n, int8_t *g) {
   if (v < 0) return false;
   long long q = v / kBiasRadixU;
   g[0] = (int8_t)(uint8_t)(v % kBiasRadixU);
@@ -98,9 +98,72 @@ static bool offset_digits(long long v, int n, int8_t *g) {
   return q == 0;
 }
 // 8-row constant tile [8 x ncols] whose rows are all `row`, in the panel layout ([ncols/16][8][16])
-static void const_tile(int8_t *dst, int ncols, const int8_t *row) {
+void const_tile(int8_t *dst, int ncols, const int8_t *row) {
   for (int c = 0; c < ncols; ++c)
     for (int r = 0; r < 8; ++r) dst[(size_t)(c / 16) * 128 + r * 16 + (c % 16)] = row[c];
+}
+
+
+long long digit_capacity(int ncols) { return (long long)kBiasRadixU - 1 + (long long)kBiasRadixU * 255 * (ncols - 1); }
+
+// RQM_FP constants of one stage (requantisation on the FMA pipe, fused_kernel.cuh): an accumulator offset INIT with
+// INIT*mult == rnd (mod 2^shift), INIT > |acc|max (bnd), INIT + |acc|max < 2^24, and C = (rnd - INIT*mult)/2^shift + add + 128
+// with C < 0 and 257 - C < 2^24 (the ITAmax distance constant m + 129 - C must stay in the linear f32 range); the offset plus
+// the largest bias (bmax) must fit the unsigned digits of the stage's digit K steps (cap).
+bool plan_fp_stage(const Rq &r, long long bnd, long long bmax, long long cap, FRq *out) {
+  if (r.mult <= 0 || r.shift < 1 || r.shift > 30) return false;
+  int t = 0;
+  while (((r.mult >> t) & 1) == 0) ++t;
+  const int mb = r.shift - t;                                  // INIT is determined modulo 2^mb
+  const long long rnd = r.rnd;
+  if (mb < 0 || (rnd & ((1LL << t) - 1))) return false;
+  const long long lo = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
+  long long init = lo;
+  if (mb > 0) {
+    const long long mo = r.mult >> t, mask = (1LL << mb) - 1;
+    unsigned long long inv = 1;
+    for (int k = 0; k < 6; ++k) inv = inv * (2ULL - (unsigned long long)mo * inv);   // Newton: inverse of the odd part modulo 2^64
+    const long long k0 = (long long)((((unsigned long long)(rnd >> t) & mask) * (inv & mask)) & mask);
+    init = lo + ((k0 - lo) & mask);                            // smallest value >= lo congruent to k0
+  }
+  if ((init * r.mult - rnd) & ((1LL << r.shift) - 1)) return false;
+  const long long Cc = (rnd - init * r.mult) / (1LL << r.shift) + r.add + 128;
+  if (init + bnd >= (1LL << 24) || init + bmax > cap || Cc >= 0 || 257 - Cc >= (1LL << 24)) return false;
+  out->init = (int32_t)init;
+  out->negc = (int32_t)-Cc;
+  out->fb = ldexpf((float)r.mult, -r.shift);
+  out->fc = ldexpf((float)Cc, -149);
+  return (long long)ldexpf(out->fc, 149) == Cc;
+}
+
+// The fp32 requant form on offset accumulators.  form 2 (RQM_TORCH_FP2, two FFMAs per element): the offset is a power of
+// two; form 1 (RQM_TORCH_FP, three): any INIT > |acc|max that fits.
+bool plan_torch_stage(const Rq &r, long long bnd, long long bmax, long long cap, int form, FRq *out) {
+  long long init = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
+  if (form == 2)
+    while (init & (init - 1)) init += init & -init;          // round up to a power of two
+  const long long Cc = (long long)r.add + 128;
+  // (zp + 128 must be even: the final FFMA rounds t + zp + 128 to nearest-even, which equals rne(t) + zp + 128 on ties only
+  //  then; the reference's zero-points are all 0 -- symmetric quantisation, layers.py:10-21)
+  if (init + bnd >= (1LL << 24) || init + bmax > cap || Cc < 0 || (Cc & 1) || Cc >= (1LL << 23) || !(r.eff > 0.f)) return false;
+  out->init = (int32_t)init;
+  out->negc = (int32_t)-Cc;
+  out->fc = ldexpf((float)Cc, -149);
+  if (form == 2) {
+    // fb = eff * 2^85, eff = -INIT * eff * 2^-64 (exact: INIT is a power of two); both must be normal and exact scalings
+    const float b1 = ldexpf(r.eff, 85), c1 = -ldexpf(r.eff * (float)init, -64);
+    if (!isfinite(b1) || ldexpf(b1, -85) != r.eff || !(fabsf(c1) >= 1e-30f) || -ldexpf(c1, 64) != r.eff * (float)init || r.eff < 1e-9f ||
+        r.eff > 256.f)
+      return false;
+    out->fb = b1;
+    out->eff = c1;
+  } else {
+    const float effs = ldexpf(r.eff, 23);
+    if (!isfinite(effs) || ldexpf(effs, -23) != r.eff) return false;
+    out->fb = -ldexpf((float)init, -23);
+    out->eff = effs;
+  }
+  return true;
 }
 
 int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
@@ -180,36 +243,10 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   FRq fp[6] = {};
   bool fp_ok = (mode == RQM_INT_HI);
   if (const char *e = getenv("ITA_FUSED_FP")) fp_ok = fp_ok && atoi(e) != 0;    // tuning knob: 0 = keep the integer forms
-  auto digit_cap = [](int ncols) { return (long long)kBiasRadixU - 1 + (long long)kBiasRadixU * 255 * (ncols - 1); };
-  const long long cap32 = digit_cap(kBiasK), cap64 = digit_cap(kBiasKO), cap96 = digit_cap(96);
+  const long long cap32 = digit_capacity(kBiasK), cap64 = digit_capacity(kBiasKO), cap96 = digit_capacity(96);
   for (int i = 0; i < 6 && fp_ok; ++i) {
-    const Rq &r = h->rq_host[stages[i] * h->H];
-    if (r.mult <= 0 || r.shift < 1 || r.shift > 30) { fp_ok = false; break; }
-    int t = 0;
-    while (((r.mult >> t) & 1) == 0) ++t;
-    const int mb = r.shift - t;                                  // INIT is determined modulo 2^mb
-    const long long rnd = r.rnd;
-    if (mb < 0 || (rnd & ((1LL << t) - 1))) { fp_ok = false; break; }
-    const long long bnd = bound[i];
-    const long long lo = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
-    long long init = lo;
-    if (mb > 0) {
-      const long long mo = r.mult >> t, mask = (1LL << mb) - 1;
-      unsigned long long inv = 1;
-      for (int k = 0; k < 6; ++k) inv = inv * (2ULL - (unsigned long long)mo * inv);   // Newton: inverse of the odd part modulo 2^64
-      const long long k0 = (long long)((((unsigned long long)(rnd >> t) & mask) * (inv & mask)) & mask);
-      init = lo + ((k0 - lo) & mask);                            // smallest value >= lo congruent to k0
-    }
-    if ((init * r.mult - rnd) & ((1LL << r.shift) - 1)) { fp_ok = false; break; }
-    const long long Cc = (rnd - init * r.mult) / (1LL << r.shift) + r.add + 128;
     // the stage's digit capacity: bias + offset (projections: one step; output projection, logits: two; context: one)
-    const long long cap = (i == 3 || i == 5) ? cap64 : cap32;
-    if (init + bnd >= (1LL << 24) || init + bmaxs[i] > cap || Cc >= 0 || 257 - Cc >= (1LL << 24)) { fp_ok = false; break; }
-    fp[i].init = (int32_t)init;
-    fp[i].negc = (int32_t)-Cc;
-    fp[i].fb = ldexpf((float)r.mult, -r.shift);
-    fp[i].fc = ldexpf((float)Cc, -149);
-    if ((long long)ldexpf(fp[i].fc, 149) != Cc) fp_ok = false;
+    fp_ok = plan_fp_stage(h->rq_host[stages[i] * h->H], bound[i], bmaxs[i], (i == 3 || i == 5) ? cap64 : cap32, &fp[i]);
   }
   if (fp_ok) mode = RQM_FP;
   // ---- the fp32 requant form on offset accumulators.  RQM_TORCH_FP2 (two FFMAs per element) needs every stage's offset to
@@ -222,32 +259,8 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     for (int form = want2 ? 2 : 1; form >= 1 && allow && mode == RQM_TORCH; --form) {
       bool ok = true;
       for (int i = 0; i < 6 && ok; ++i) {
-        const Rq &r = h->rq_host[stages[i] * h->H];
-        const long long bnd = bound[i];
-        long long init = (bnd + 1 > (1LL << 20)) ? bnd + 1 : (1LL << 20);
-        if (form == 2)
-          while (init & (init - 1)) init += init & -init;          // round up to a power of two
         const long long cap = (i == 3) ? (form == 2 ? cap96 : cap64) : (i == 5 ? cap64 : cap32);
-        const long long Cc = (long long)r.add + 128;
-        // (zp + 128 must be even: the final FFMA rounds t + zp + 128 to nearest-even, which equals rne(t) + zp + 128 on ties only
-        //  then; the reference's zero-points are all 0 -- symmetric quantisation, layers.py:10-21)
-        if (init + bnd >= (1LL << 24) || init + bmaxs[i] > cap || Cc < 0 || (Cc & 1) || Cc >= (1LL << 23) || !(r.eff > 0.f)) { ok = false; break; }
-        fp[i].init = (int32_t)init;
-        fp[i].negc = (int32_t)-Cc;
-        fp[i].fc = ldexpf((float)Cc, -149);
-        if (form == 2) {
-          // fb = eff * 2^85, eff = -INIT * eff * 2^-64 (exact: INIT is a power of two); both must be normal and exact scalings
-          const float b1 = ldexpf(r.eff, 85), c1 = -ldexpf(r.eff * (float)init, -64);
-          if (!isfinite(b1) || ldexpf(b1, -85) != r.eff || !(fabsf(c1) >= 1e-30f) || -ldexpf(c1, 64) != r.eff * (float)init ||
-              r.eff < 1e-9f || r.eff > 256.f) { ok = false; break; }
-          fp[i].fb = b1;
-          fp[i].eff = c1;
-        } else {
-          const float effs = ldexpf(r.eff, 23);
-          if (!isfinite(effs) || ldexpf(effs, -23) != r.eff) { ok = false; break; }
-          fp[i].fb = -ldexpf((float)init, -23);
-          fp[i].eff = effs;
-        }
+        ok = plan_torch_stage(h->rq_host[stages[i] * h->H], bound[i], bmaxs[i], cap, form, &fp[i]);
       }
       if (ok) mode = form == 2 ? RQM_TORCH_FP2 : RQM_TORCH_FP;
     }

@@ -407,7 +407,8 @@ __device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
 //   panel      shared-memory panel buffer of a [kS x *] matrix (nullptr: do not store to smem)
 //   col        first of the 32 columns inside that matrix
 //   grow       global pointer to the first of these 32 columns (natural layout) or nullptr
-template <int MODE, int ALT>
+//   RELU       max(0, .) on the requantised value (FFN fc1): the sign bytes are replicated into a mask by one PRMT
+template <int MODE, int ALT, bool RELU = false>
 __device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const FRq &r, int8_t *panel, int row, int col, int8_t *grow) {
 #pragma unroll
   for (int j = 0; j < 32; j += 16) {
@@ -418,11 +419,23 @@ __device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const F
       if constexpr (rqm_offset(MODE)) {
         rq_off_bits2<MODE>(v[j + q * 4], v[j + q * 4 + 1], r, y[0], y[1]);
         rq_off_bits2<MODE>(v[j + q * 4 + 2], v[j + q * 4 + 3], r, y[2], y[3]);
-        w[q] = pack_u8x4(y[0], y[1], y[2], y[3]) ^ 0x80808080u;
+        const uint32_t u = pack_u8x4(y[0], y[1], y[2], y[3]);              // y + 128 per byte
+        if constexpr (RELU) {
+          uint32_t m;                                                       // 0xFF where y >= 0 (msb of the biased byte)
+          asm("prmt.b32 %0, %1, %1, 0xba98;" : "=r"(m) : "r"(u));
+          w[q] = (u ^ 0x80808080u) & m;
+        } else {
+          w[q] = u ^ 0x80808080u;
+        }
       } else {
 #pragma unroll
         for (int i = 0; i < 4; ++i) y[i] = rq_apply<MODE, ALT>((int)v[j + q * 4 + i], r, i);
         w[q] = pack_s8x4(y[0], y[1], y[2], y[3]);
+        if constexpr (RELU) {
+          uint32_t m;                                                       // 0xFF where y < 0
+          asm("prmt.b32 %0, %1, %1, 0xba98;" : "=r"(m) : "r"(w[q]));
+          w[q] &= ~m;
+        }
       }
     }
     const uint4 o = make_uint4(w[0], w[1], w[2], w[3]);
@@ -1087,6 +1100,15 @@ __global__ void __launch_bounds__((Cfg<E, P>::THREADS), 1) k_ita_fused(const __g
     tmem_dealloc<512>(tmem_base);
   }
 }
+
+// ---------------------------------------------------------------------------------------------------- host-side planning (fused.cu)
+long long digit_capacity(int ncols);
+bool plan_fp_stage(const Rq &r, long long bnd, long long bmax, long long cap, FRq *out);
+bool plan_torch_stage(const Rq &r, long long bnd, long long bmax, long long cap, int form, FRq *out);
+bool bias_digits(int32_t b, int8_t *g);                      // kBiasK signed radix-127 digits
+bool offset_digits(long long v, int n, int8_t *g);           // n unsigned radix-255 digits
+void const_tile(int8_t *dst, int ncols, const int8_t *row);  // 8-row constant tile in the panel layout
+int make_x_tensor_map(CUtensorMap *map, const void *x, long long rows, int row_bytes);
 
 // ---------------------------------------------------------------------------------------------------- instantiation
 typedef void (*KernelFn)(const CUtensorMap, const FusedParams);

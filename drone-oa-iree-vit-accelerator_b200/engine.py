@@ -181,14 +181,48 @@ class ITAEngine:
                                       C.c_void_p(out.data_ptr()), batch, _stream_ptr(stream, self.device)), "ita_mha_step")
         return out
 
-    def ffn(self, x: torch.Tensor, want_f1: bool = False, stream: Optional[torch.cuda.Stream] = None):
+    @property
+    def ffn_fused_supported(self) -> bool:
+        return bool(self.lib.ita_ffn_fused_supported(self._h))
+
+    def ffn_fused_unsupported_reason(self) -> str:
+        return "" if self.ffn_fused_supported else self.lib.ita_last_error().decode()
+
+    def ffn(self, x: torch.Tensor, want_f1: bool = False, stream: Optional[torch.cuda.Stream] = None,
+            path: int = L.PATH_AUTO, out: Optional[torch.Tensor] = None):
+        """FFN block fc2(relu(fc1(x))), int8 in / int8 out.  ``path``: PATH_FUSED = the tcgen05 kernel (F1 stays on chip),
+        PATH_STAGED = CUDA-core GEMMs, PATH_AUTO = fused when supported."""
         B = self._batch_of(x)
-        f2 = torch.empty_like(x)
+        f2 = torch.empty_like(x) if out is None else out
         f1 = torch.empty((B, self.S, self.F), dtype=torch.int8, device=self.device) if want_f1 else None
-        L.check(self.lib.ita_ffn_forward(self._h, C.c_void_p(x.data_ptr()),
-                                         C.c_void_p(f1.data_ptr() if f1 is not None else None),
-                                         C.c_void_p(f2.data_ptr()), B, _stream_ptr(stream, self.device)), "ita_ffn_forward")
+        L.check(self.lib.ita_ffn_forward_path(self._h, C.c_void_p(x.data_ptr()),
+                                              C.c_void_p(f1.data_ptr() if f1 is not None else None),
+                                              C.c_void_p(f2.data_ptr()), B, path, _stream_ptr(stream, self.device)),
+                "ita_ffn_forward")
         return (f1, f2) if want_f1 else f2
+
+    def layer_params(self, s_attn_in: float, s_attn_out: float, s_ffn_in: float, s_ffn_out: float, ln1_w, ln1_b, ln2_w, ln2_b,
+                     eps: float = 1e-5):
+        """Bundle the float side of an encoder layer (scales of the four stubs, the two LayerNorms) for ``layer()``."""
+        t = [torch.as_tensor(a, dtype=torch.float32).to(self.device).contiguous() for a in (ln1_w, ln1_b, ln2_w, ln2_b)]
+        for a in t:
+            if a.numel() != self.E:
+                raise ValueError(f"LayerNorm parameters must have {self.E} elements")
+        lp = L.LayerParams(float(s_attn_in), float(s_attn_out), float(s_ffn_in), float(s_ffn_out), float(eps),
+                           *(C.c_void_p(a.data_ptr()) for a in t))
+        lp._keep = t
+        return lp
+
+    def layer(self, x: torch.Tensor, lp, out: Optional[torch.Tensor] = None, stream: Optional[torch.cuda.Stream] = None):
+        """One encoder layer, f32 cuda [B,S,E] -> f32 cuda [B,S,E] (reference QAT/model.py:100-113)."""
+        if x.dtype != torch.float32 or not x.is_cuda or not x.is_contiguous() or x.dim() != 3 or \
+                tuple(x.shape[1:]) != (self.S, self.E):
+            raise ValueError(f"layer() expects a contiguous float32 cuda tensor [B,{self.S},{self.E}]")
+        y = torch.empty_like(x) if out is None else out
+        L.check(self.lib.ita_encoder_layer_forward(self._h, C.byref(lp), C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
+                                                   int(x.shape[0]), _stream_ptr(stream, self.device)),
+                "ita_encoder_layer_forward")
+        return y
 
 
 def quantize(x: torch.Tensor, scale: float) -> torch.Tensor:
@@ -201,6 +235,27 @@ def quantize(x: torch.Tensor, scale: float) -> torch.Tensor:
         L.check(L.load().ita_quantize_f32(C.c_void_p(x.data_ptr()), C.c_void_p(q.data_ptr()), x.numel(), float(scale),
                                           _stream_ptr(None, x.device)), "ita_quantize_f32")
     return q
+
+
+def residual_layernorm(x: torch.Tensor, q: torch.Tensor, q_scale: float, weight: torch.Tensor, bias: torch.Tensor, eps: float = 1e-5,
+                       quant_scale: Optional[float] = None):
+    """``LayerNorm(x + q_scale * q)`` (dequant stub + ``self.add.add`` + LayerNorm of QAT/model.py:104-106) and, when
+    ``quant_scale`` is given, the next block's quant stub on the result.  Returns ``y`` or ``(y, y_q)``."""
+    if not (x.is_cuda and x.dtype == torch.float32 and q.dtype == torch.int8 and x.shape == q.shape):
+        raise ValueError("residual_layernorm expects float32 x and int8 q of the same shape on a CUDA device")
+    x, q = x.contiguous(), q.contiguous()
+    E = int(x.shape[-1])
+    w = weight.to(x.device, torch.float32).contiguous()
+    b = bias.to(x.device, torch.float32).contiguous()
+    y = torch.empty_like(x)
+    yq = torch.empty(x.shape, dtype=torch.int8, device=x.device) if quant_scale is not None else None
+    with torch.cuda.device(x.device):
+        L.check(L.load().ita_residual_layernorm(C.c_void_p(x.data_ptr()), C.c_void_p(q.data_ptr()), float(q_scale),
+                                                C.c_void_p(w.data_ptr()), C.c_void_p(b.data_ptr()), float(eps),
+                                                C.c_void_p(y.data_ptr()), C.c_void_p(yq.data_ptr() if yq is not None else None),
+                                                float(quant_scale or 0.0), x.numel() // E, E, _stream_ptr(None, x.device)),
+                "ita_residual_layernorm")
+    return y if yq is None else (y, yq)
 
 
 def dequantize(q: torch.Tensor, scale: float) -> torch.Tensor:

@@ -31,10 +31,17 @@
  *   ita_ffn_forward
  *       ITAFeedForward_QAT.forward  models/ITA/QAT/layers.py:61-75 == golden feedforward_layer
  *       tests/export_and_validation_W_B.py:544-553.
+ *   ita_residual_layernorm, ita_encoder_layer_forward
+ *       the float ops between the int8 blocks and the encoder-layer loop body
+ *       models/ITA_single_layer_upsample_shuffle/QAT/model.py:100-113.
  *   ita_quantize_f32 / ita_dequantize_s8
  *       the QuantStub / DeQuantStub at the float boundary of the operator   models/ITA/QAT/layers.py:103,126.
  *
- * Threading: a handle may be used from one host thread at a time; distinct handles are independent.  All device work
+ * Threading: a handle may be used from one host thread at a time; distinct handles are independent.  The *_host entry
+ * points stage through ONE per-handle device buffer: at most one ita_mha_forward_host[_async] call per handle may be in
+ * flight (use one handle per stream to overlap calls, as bench.py does); the first call of a larger batch reallocates
+ * that buffer, which synchronises the device.  Device-side time-outs of the fused kernels (every in-kernel wait is
+ * bounded) are reported by ita_mha_sync_check and by the synchronous entry points, not by the asynchronous ones.  All device work
  * of a call is enqueued on the CUDA stream passed in (a cudaStream_t cast to void*; NULL = the legacy default stream)
  * and, except for the *_host entry points, the call returns without synchronising.
  */
@@ -143,6 +150,33 @@ ITA_API int ita_mha_step(ita_mha_handle *h, int32_t step, const void *in0, const
 
 /* FFN block: x_dev [batch,S,E] s8 -> f2_dev [batch,S,E] s8; f1_dev ([batch,S,F] s8, post-ReLU) may be NULL. */
 ITA_API int ita_ffn_forward(ita_mha_handle *h, const int8_t *x_dev, int8_t *f1_dev, int8_t *f2_dev, int64_t batch, void *cuda_stream);
+
+/* same with an explicit path: ITA_PATH_FUSED = the tcgen05 FFN kernel (F1 stays in shared memory; f1_dev, when given, is an
+ * extra copy), ITA_PATH_STAGED = two CUDA-core GEMM kernels, ITA_PATH_AUTO = fused when ita_ffn_fused_supported(). */
+ITA_API int ita_ffn_forward_path(ita_mha_handle *h, const int8_t *x_dev, int8_t *f1_dev, int8_t *f2_dev, int64_t batch, int32_t path,
+                                 void *cuda_stream);
+ITA_API int ita_ffn_fused_supported(const ita_mha_handle *h);
+
+/* The float stages between the two int8 blocks of an encoder layer (reference
+ * models/ITA_single_layer_upsample_shuffle/QAT/model.py:104-106,111-113: dequant stub, `self.add.add`, LayerNorm, and the
+ * next block's quant stub), one pass:  y = LayerNorm(x + q_scale * q) * ln_w + ln_b  over the last dimension E (64 or 128);
+ * yq = sat8(rne(y / yq_scale)) when yq_dev is not NULL.  All DEVICE pointers; x/y [rows,E] f32, q/yq [rows,E] s8. */
+ITA_API int ita_residual_layernorm(const float *x_dev, const int8_t *q_dev, float q_scale, const float *ln_w_dev, const float *ln_b_dev,
+                                   float eps, float *y_dev, int8_t *yq_dev, float yq_scale, int64_t rows, int32_t E, void *cuda_stream);
+
+/* One encoder layer of ITAViTLSTM, f32 tokens in -> f32 tokens out: the loop body of ITALSTMNetVIT_QAT.forward
+ * (models/ITA_single_layer_upsample_shuffle/QAT/model.py:100-113) -- quant stub, int8 attention, dequant + residual +
+ * LayerNorm, quant stub, int8 FFN, dequant + residual + LayerNorm.  The handle must carry FFN parameters (F > 0). */
+typedef struct ita_layer_params {
+  float s_attn_in;    /* attention_blocks[i].quant.scale        */
+  float s_attn_out;   /* attention_blocks[i].out_proj.scale     */
+  float s_ffn_in;     /* ffn_blocks[i].quant.scale              */
+  float s_ffn_out;    /* ffn_blocks[i].fc2.scale                */
+  float ln_eps;       /* nn.LayerNorm eps (1e-5)                */
+  const float *ln1_w, *ln1_b, *ln2_w, *ln2_b;   /* DEVICE pointers, [E]: norms1[i], norms2[i] */
+} ita_layer_params;
+ITA_API int ita_encoder_layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x_dev, float *y_dev, int64_t batch,
+                                      void *cuda_stream);
 
 /* float boundary: q = sat8(rne(x / scale)),  y = scale * q   (n elements, DEVICE pointers) */
 ITA_API int ita_quantize_f32(const float *x_dev, int8_t *q_dev, int64_t n, float scale, void *cuda_stream);
