@@ -243,3 +243,24 @@ def test_quantize_fixture_definition():
         with np.errstate(over="ignore", invalid="ignore"):
             y = np.clip(np.rint(x * inv), -128, 127).astype(np.int8)
         assert np.array_equal(y, q), float(s)
+
+
+def test_layer_oracle_vs_model_fixture(R, ita):
+    """Encoder layer (quant, int8 attention, residual + LayerNorm, quant, int8 FFN, residual + LayerNorm; reference
+    QAT/model.py:100-113) restated in the oracle vs the full converted-model trace: int8 stages bit-exact, float stages
+    within 2e-6 (LayerNorm summation order)."""
+    import sys
+    sys.path.insert(0, GOLDEN)
+    import seeded
+    q = np.load(os.path.join(GOLDEN, "qat_model_E64.npz"))
+    p = _block_params(R, q, "b0_", R.ROUND_TORCH_RNE_F32)
+    f = _ffn_params(R, q)
+    p.F, p.Wff, p.Wff2, p.Bff, p.Bff2 = f.F, f.Wff, f.Wff2, f.Bff, f.Bff2
+    p.eff[R.ST_FC1], p.eff[R.ST_FC2], p.mult[R.ST_RELU] = f.eff[R.ST_FC1], f.eff[R.ST_FC2], 0
+    ln = [seeded.float_param(k, (64,)) for k in ("norms1.0.weight", "norms1.0.bias", "norms2.0.weight", "norms2.0.bias")]
+    o = R.layer_forward(p, q["attn_in"], float(q["b0_s_x"]), float(q["b0_out_proj_sout"]), float(q["b0_fc1_sin"]),
+                        float(q["b0_fc2_sout"]), *ln)
+    assert np.array_equal(o["xq"], q["b0_x"]) and np.array_equal(o["yq"], q["b0_out_proj_out"].reshape(o["yq"].shape))
+    assert np.abs(o["x1"] - q["norm1_out"]).max() <= 2e-6
+    assert np.array_equal(o["x1q"], q["b0_ffn_x"]) and np.array_equal(o["f2q"], q["b0_fc2_out"])
+    assert np.abs(o["y"] - q["norm2_out"]).max() <= 2e-6

@@ -11,4 +11,6 @@ echo "== modes, -DITA_NO_F32X2"; ITA_B200_LIB=$PWD/build_tools/libita_b200.so py
 python bench.py --steps 20 --warmup 5 > gpurun_out/r2a_bench.json 2> gpurun_out/r2a_bench.err; echo "bench exit $?"; cat gpurun_out/r2a_bench.json
 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/r2a_bench_ref.json 2> gpurun_out/r2a_bench_ref.err; cat gpurun_out/r2a_bench_ref.json
 python bench.py --config c2_e128 --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/r2a_bench_e128.json 2> gpurun_out/r2a_bench_e128.err; cat gpurun_out/r2a_bench_e128.json
-tail -3 gpurun_out/r2a_bench.err gpurun_out/r2a_bench_e128.err
+python bench.py --config c2_ffn --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/r2a_bench_ffn.json 2> gpurun_out/r2a_bench_ffn.err; cat gpurun_out/r2a_bench_ffn.json
+python bench.py --config c2_stack --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/r2a_bench_stack.json 2> gpurun_out/r2a_bench_stack.err; cat gpurun_out/r2a_bench_stack.json
+tail -3 gpurun_out/r2a_bench.err gpurun_out/r2a_bench_e128.err gpurun_out/r2a_bench_ffn.err gpurun_out/r2a_bench_stack.err
