@@ -54,6 +54,8 @@ SYMBOLS = {
     "ita_mha_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "ita_mha_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "ita_mha_forward_host_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
+    "ita_mha_forward_host_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_int32, C.c_void_p]),
+    "ita_mha_describe": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "ita_mha_forward_stages": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(MhaStages), C.c_void_p]),
     "ita_mha_forward_fused_debug": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(MhaStages), C.c_void_p]),
     "ita_mha_sync_check": (C.c_int, [C.c_void_p, C.c_void_p]),

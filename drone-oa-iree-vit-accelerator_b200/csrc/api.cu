@@ -332,6 +332,54 @@ static int forward_host_impl(ita_mha_handle *h, const int8_t *x_host, int8_t *y_
   return rc;
 }
 
+/* f32 host tokens in -> f32 host tokens out: quant stub, attention, dequant stub (ITASelfAttention_QAT.forward,
+ * models/ITA/QAT/layers.py:101-127) on caller-owned HOST buffers, synchronous -- the contract of the IREE dispatch symbol
+ * (csrc/ita_dispatch_shim.c). */
+int ita_mha_forward_host_f32(ita_mha_handle *h, const float *x_host, float *y_host, int64_t batch, float s_in, float s_out, int32_t path,
+                             void *cuda_stream) {
+  int rc = check_fwd_args("ita_mha_forward_host_f32", h, x_host, y_host, batch);
+  if (rc) return rc;
+  if (!(s_in > 0.f)) {
+    set_error("ita_mha_forward_host_f32: the input scale must be positive");
+    return ITA_ERR_INVALID;
+  }
+  if (batch == 0) return ITA_OK;
+  DeviceGuard guard(h->device);
+  cudaStream_t s = (cudaStream_t)cuda_stream;
+  const size_t n = (size_t)h->S * h->E * (size_t)batch, need = 6 * n;
+  if (h->io_bytes < need) {
+    if (h->io_dev) cudaFree(h->io_dev);
+    h->io_dev = nullptr;
+    h->io_bytes = 0;
+    if (cudaMalloc(&h->io_dev, need) != cudaSuccess) {
+      cudaGetLastError();
+      set_error("ita_mha_forward_host_f32: cudaMalloc(%zu) failed", need);
+      return ITA_ERR_NOMEM;
+    }
+    h->io_bytes = need;
+  }
+  float *fd = reinterpret_cast<float *>(h->io_dev);
+  int8_t *xq = h->io_dev + 4 * n, *yq = xq + n;
+  ITA_CUDA_TRY(cudaMemcpyAsync(fd, x_host, 4 * n, cudaMemcpyHostToDevice, s));
+  if ((rc = launch_quantize(fd, xq, (int64_t)n, s_in, s))) return rc;
+  if ((rc = forward_dev(h, xq, yq, batch, path, s))) return rc;
+  if ((rc = launch_dequantize(yq, fd, (int64_t)n, s_out, s))) return rc;
+  ITA_CUDA_TRY(cudaMemcpyAsync(y_host, fd, 4 * n, cudaMemcpyDeviceToHost, s));
+  return check_abort(h, s, "ita_mha_forward_host_f32");
+}
+
+/* Human-readable description of what the handle will run (kernel family, frames in flight, requant form). */
+int ita_mha_describe(const ita_mha_handle *h, char *buf, int64_t len) {
+  if (!h || !buf || len <= 0) {
+    set_error("ita_mha_describe: bad arguments");
+    return ITA_ERR_INVALID;
+  }
+  std::string d = describe_fused(h) + "; " + describe_ffn(h);
+  strncpy(buf, d.c_str(), (size_t)len - 1);
+  buf[len - 1] = 0;
+  return ITA_OK;
+}
+
 int ita_mha_forward_stages(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64_t batch, const ita_mha_stages *stages,
                            void *cuda_stream) {
   if (!h || (batch > 0 && !x_dev) || batch < 0) {

@@ -99,6 +99,8 @@ int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, cons
 int ffn_plan_create(ita_mha_handle *h, const ita_mha_desc *d);     // sets h->ffn or h->ffn_reason
 void ffn_plan_destroy(ita_mha_handle *h);
 int ffn_fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *f1, int8_t *f2, int64_t B, cudaStream_t s);
+std::string describe_fused(const ita_mha_handle *h);   // fused.cu
+std::string describe_ffn(const ita_mha_handle *h);     // ffn.cu
 // layer.cu
 int launch_resid_ln(const float *x, const int8_t *q, float sq, const float *gamma, const float *beta, float eps, float *y, int8_t *yq,
                     float s_next, int64_t rows, int E, cudaStream_t s);

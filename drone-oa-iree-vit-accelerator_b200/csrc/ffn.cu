@@ -168,6 +168,17 @@ int ffn_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   return ITA_OK;
 }
 
+const char *rqm_name(int mode);   // fused.cu
+
+std::string describe_ffn(const ita_mha_handle *h) {
+  char b[256];
+  if (!h->ffn) snprintf(b, sizeof(b), "ffn: staged CUDA-core kernels (%s)", h->ffn_reason.c_str());
+  else
+    snprintf(b, sizeof(b), "ffn: k_ita_ffn<E=%d,F=%d> %s, %d frames in flight per SM, %d threads, %d B smem", h->ffn->E, h->ffn->F,
+             rqm_name(h->ffn->mode), h->ffn->slots, h->ffn->threads, h->ffn->smem_bytes);
+  return b;
+}
+
 void ffn_plan_destroy(ita_mha_handle *h) {
   if (h->ffn) {
     cudaFree(h->ffn->wpanels);

@@ -386,6 +386,21 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   return ITA_OK;
 }
 
+static const char *const kModeNames[] = {"RQM_INT_HI", "RQM_INT_GEN", "RQM_TORCH", "RQM_FP", "RQM_TORCH_FP", "RQM_TORCH_FP2"};
+const char *rqm_name(int mode) { return mode >= 0 && mode <= 5 ? kModeNames[mode] : "?"; }
+
+std::string describe_fused(const ita_mha_handle *h) {
+  char b[256];
+  if (!h->fused) {
+    snprintf(b, sizeof(b), "attention: staged CUDA-core kernels (%s)", h->fused_reason.c_str());
+  } else {
+    const FusedPlan *pl = h->fused;
+    snprintf(b, sizeof(b), "attention: k_ita_fused<E=%d,P=%d> %s softmax=%d alt=%d, %d frame(s) in flight per SM, %d threads, %d B smem",
+             pl->E, pl->P, rqm_name(pl->mode), pl->softmax, pl->alt, pl->slots, pl->threads, pl->smem_bytes);
+  }
+  return b;
+}
+
 void fused_plan_destroy(ita_mha_handle *h) {
   if (h->fused) {
     cudaFree(h->fused->wpanels);

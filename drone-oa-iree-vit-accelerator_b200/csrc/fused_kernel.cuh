@@ -598,8 +598,12 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
   const int mp = min(max(zmax, 0), 255);          // m + 128
   bool fast = false;
 #ifndef ITA_FP_NOFAST
-  if constexpr (!DUMP) fast = allow_fast && __all_sync(0xffffffffu, zmax <= 255 && zmax >= 9);
+  if constexpr (!DUMP) fast = allow_fast && __all_sync(0xffffffffu, zmax >= 9);
 #endif
+  // rows whose maximum saturates high (common with real scales: the observers put the top of the logit range at 127) keep the
+  // one-FFMA distance with the CLAMPED maximum: an element that saturates as well then gets d + 1 <= 0, which one signed
+  // max(., 1) repairs (any pattern with the sign bit set, -0.0 included, is a negative int).  Warp-uniform choice.
+  const bool sat = !__all_sync(0xffffffffu, zmax <= 255);
   uint32_t sum = 0;
   auto store16 = [&](int g, int j, const uint4 &ov) {
     *reinterpret_cast<uint4 *>(k_buf + ((HALF * 64 + g * 32 + j) >> 4) * (kS * 16) + row * 16) = ov;
@@ -615,6 +619,9 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
     const int k2 = k2raw + (int)odd;
     const float c2 = __int_as_float(k2 >= 0 ? k2 : (int)(0x80000000u | (uint32_t)(-k2))), nfb = -rq.fb;
     const uint32_t one = 512u << odd;
+    const int dmin = 1 + (int)odd;
+    auto passes = [&](auto clamp_tag) {
+    constexpr bool CLAMP = decltype(clamp_tag)::value;
     // two distances per FFMA2
     auto dist2 = [&](uint32_t v0, uint32_t v1, uint32_t &d0, uint32_t &d1) {
 #ifdef ITA_NO_F32X2
@@ -648,6 +655,10 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
       d0 = (uint32_t)i0;
       d1 = (uint32_t)i1;
 #endif
+      if constexpr (CLAMP) {
+        d0 = (uint32_t)max((int)d0, dmin);
+        d1 = (uint32_t)max((int)d1, dmin);
+      }
     };
     tmem_walk<2>(addr,
                  [&](auto, const uint32_t(&v)[32]) {
@@ -681,6 +692,9 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
                    }
                  },
                  release);
+    };   // passes
+    if (sat) passes(std::true_type{});
+    else passes(std::false_type{});
   } else {
     auto dist = [&](uint32_t v) -> uint32_t { return (uint32_t)(mp - min(max(rq_off_bits<MODE>(v, rq), 0), 255)); };
     tmem_walk<2>(addr,

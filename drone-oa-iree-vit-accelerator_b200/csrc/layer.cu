@@ -13,55 +13,72 @@ namespace ita {
 
 // y = LayerNorm(x + sq * q) * gamma + beta over the last dim (E = 32 * VEC); optionally yq = sat8(rne(y / s_next)).
 // The dequantise (one fp32 multiply) and the residual add (one fp32 add) are kept as two roundings, as in the reference.
+// Each warp takes kRowsPerWarp consecutive token rows and issues all of their loads before the first reduction, so that
+// ~2 KB per warp are in flight (one row alone is 256 - 512 B: latency-bound at 40 % of the HBM rate, measured).
+constexpr int kRowsPerWarp = 4;
 template <int VEC>
 __global__ void __launch_bounds__(256) k_resid_ln(const float *__restrict__ x, const int8_t *__restrict__ q, float sq,
                                                   const float *__restrict__ gamma, const float *__restrict__ beta, float eps,
                                                   float *__restrict__ y, int8_t *__restrict__ yq, float inv_next, long long rows) {
-  constexpr int E = 32 * VEC;
+  constexpr int E = 32 * VEC, R = kRowsPerWarp;
   const int lane = threadIdx.x & 31;
-  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= rows) return;
-  float v[VEC];
-  const float *xr = x + row * E + lane * VEC;
-  const int8_t *qr = q + row * E + lane * VEC;
-  if constexpr (VEC == 2) {
-    const float2 a = *reinterpret_cast<const float2 *>(xr);
-    const char2 b = *reinterpret_cast<const char2 *>(qr);
-    v[0] = __fadd_rn(a.x, __fmul_rn(sq, (float)b.x));
-    v[1] = __fadd_rn(a.y, __fmul_rn(sq, (float)b.y));
-  } else {
-    const float4 a = *reinterpret_cast<const float4 *>(xr);
-    const char4 b = *reinterpret_cast<const char4 *>(qr);
-    v[0] = __fadd_rn(a.x, __fmul_rn(sq, (float)b.x));
-    v[1] = __fadd_rn(a.y, __fmul_rn(sq, (float)b.y));
-    v[2] = __fadd_rn(a.z, __fmul_rn(sq, (float)b.z));
-    v[3] = __fadd_rn(a.w, __fmul_rn(sq, (float)b.w));
+  const long long row0 = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * R;
+  if (row0 >= rows) return;
+  float v[R][VEC];
+  float g[VEC], bt[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) {
+    g[i] = gamma[lane * VEC + i];
+    bt[i] = beta[lane * VEC + i];
   }
-  float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < VEC; ++i) s += v[i];
+  for (int r = 0; r < R; ++r) {
+    const long long row = row0 + r < rows ? row0 + r : rows - 1;       // tail rows re-read the last row (not stored)
+    const float *xr = x + row * E + lane * VEC;
+    const int8_t *qr = q + row * E + lane * VEC;
+    if constexpr (VEC == 2) {
+      const float2 a = *reinterpret_cast<const float2 *>(xr);
+      const char2 b = *reinterpret_cast<const char2 *>(qr);
+      v[r][0] = __fadd_rn(a.x, __fmul_rn(sq, (float)b.x));
+      v[r][1] = __fadd_rn(a.y, __fmul_rn(sq, (float)b.y));
+    } else {
+      const float4 a = *reinterpret_cast<const float4 *>(xr);
+      const char4 b = *reinterpret_cast<const char4 *>(qr);
+      v[r][0] = __fadd_rn(a.x, __fmul_rn(sq, (float)b.x));
+      v[r][1] = __fadd_rn(a.y, __fmul_rn(sq, (float)b.y));
+      v[r][2] = __fadd_rn(a.z, __fmul_rn(sq, (float)b.z));
+      v[r][3] = __fadd_rn(a.w, __fmul_rn(sq, (float)b.w));
+    }
+  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  const float mean = s * (1.0f / E);
-  float ss = 0.f;
+  for (int r = 0; r < R; ++r) {
+    float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < VEC; ++i) ss += (v[i] - mean) * (v[i] - mean);
+    for (int i = 0; i < VEC; ++i) s += v[r][i];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-  const float rstd = 1.0f / sqrtf(ss * (1.0f / E) + eps);
-  float o[VEC];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s * (1.0f / E);
+    float ss = 0.f;
 #pragma unroll
-  for (int i = 0; i < VEC; ++i) o[i] = (v[i] - mean) * rstd * gamma[lane * VEC + i] + beta[lane * VEC + i];
-  float *yr = y + row * E + lane * VEC;
-  if constexpr (VEC == 2) *reinterpret_cast<float2 *>(yr) = make_float2(o[0], o[1]);
-  else *reinterpret_cast<float4 *>(yr) = make_float4(o[0], o[1], o[2], o[3]);
-  if (yq) {
-    int8_t r[VEC];
+    for (int i = 0; i < VEC; ++i) ss += (v[r][i] - mean) * (v[r][i] - mean);
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) r[i] = (int8_t)(int)fminf(fmaxf(nearbyintf(o[i] * inv_next), -128.f), 127.f);
-    int8_t *qo = yq + row * E + lane * VEC;
-    if constexpr (VEC == 2) *reinterpret_cast<char2 *>(qo) = make_char2(r[0], r[1]);
-    else *reinterpret_cast<char4 *>(qo) = make_char4(r[0], r[1], r[2], r[3]);
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float rstd = 1.0f / sqrtf(ss * (1.0f / E) + eps);
+    if (row0 + r >= rows) continue;                                     // warp-uniform
+    float o[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) o[i] = (v[r][i] - mean) * rstd * g[i] + bt[i];
+    float *yr = y + (row0 + r) * E + lane * VEC;
+    if constexpr (VEC == 2) *reinterpret_cast<float2 *>(yr) = make_float2(o[0], o[1]);
+    else *reinterpret_cast<float4 *>(yr) = make_float4(o[0], o[1], o[2], o[3]);
+    if (yq) {
+      int8_t t[VEC];
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) t[i] = (int8_t)(int)fminf(fmaxf(nearbyintf(o[i] * inv_next), -128.f), 127.f);
+      int8_t *qo = yq + (row0 + r) * E + lane * VEC;
+      if constexpr (VEC == 2) *reinterpret_cast<char2 *>(qo) = make_char2(t[0], t[1]);
+      else *reinterpret_cast<char4 *>(qo) = make_char4(t[0], t[1], t[2], t[3]);
+    }
   }
 }
 
@@ -77,7 +94,8 @@ int launch_resid_ln(const float *x, const int8_t *q, float sq, const float *gamm
     return ITA_ERR_INVALID;
   }
   const float inv = yq ? 1.0f / s_next : 0.f;      // formed in fp32 like ATen's quantize_per_tensor
-  const unsigned blocks = (unsigned)((rows + 7) / 8);
+  const long long per_block = 8 * kRowsPerWarp;
+  const unsigned blocks = (unsigned)((rows + per_block - 1) / per_block);
   if (E == 64) k_resid_ln<2><<<blocks, 256, 0, s>>>(x, q, sq, gamma, beta, eps, y, yq, inv, rows);
   else k_resid_ln<4><<<blocks, 256, 0, s>>>(x, q, sq, gamma, beta, eps, y, yq, inv, rows);
   count_launch();

@@ -94,6 +94,12 @@ class ITAEngine:
     def fused_unsupported_reason(self) -> str:
         return "" if self.fused_supported else self.lib.ita_last_error().decode()
 
+    def describe(self) -> str:
+        """Which kernels / requant forms this engine runs (``ita_mha_describe``)."""
+        buf = C.create_string_buffer(1024)
+        L.check(self.lib.ita_mha_describe(self._h, buf, len(buf)), "ita_mha_describe")
+        return buf.value.decode()
+
     # -- helpers
     def _check_x(self, x: torch.Tensor, last: int) -> int:
         if x.dtype not in (torch.int8, torch.uint8):

@@ -128,6 +128,13 @@ ITA_API int ita_mha_forward_host(ita_mha_handle *h, const int8_t *x_host, int8_t
  * time-outs).  With two handles on two streams the H2D copies of one call overlap the D2H copies of the other. */
 ITA_API int ita_mha_forward_host_async(ita_mha_handle *h, const int8_t *x_host, int8_t *y_host, int64_t batch, int32_t path,
                                void *cuda_stream);
+/* The whole operator on HOST float buffers: y = s_out * attention(sat8(rne(x / s_in))), x/y [batch,S,E] f32
+ * (ITASelfAttention_QAT.forward with its quant / dequant stubs, models/ITA/QAT/layers.py:101-127); synchronous.  This is
+ * what the IREE dispatch symbol ITASelfAttention_workgroup(in, out) computes (csrc/ita_dispatch_shim.c). */
+ITA_API int ita_mha_forward_host_f32(ita_mha_handle *h, const float *x_host, float *y_host, int64_t batch, float s_in, float s_out,
+                                     int32_t path, void *cuda_stream);
+/* which kernels / requantisation forms this handle runs, as text (diagnostics; written into buf, NUL-terminated) */
+ITA_API int ita_mha_describe(const ita_mha_handle *h, char *buf, int64_t len);
 /* staged kernels; writes every requested intermediate (DEVICE pointers) and y_dev (may be NULL). */
 ITA_API int ita_mha_forward_stages(ita_mha_handle *h, const int8_t *x_dev, int8_t *y_dev, int64_t batch,
                            const ita_mha_stages *stages, void *cuda_stream);

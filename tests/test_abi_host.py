@@ -149,3 +149,20 @@ def test_shard_range(ita):
             assert max(sizes) - min(sizes) <= 1
     with pytest.raises(ValueError):
         ita.shard_range(4, 4, 4)
+
+
+def test_dispatch_shim_exports_reference_symbols(ita):
+    """libita_dispatch_shim*.so export the C symbol the reference's compiled model imports
+    (samples/inference_udp_FPGA_custom_dispatch/plugin/ITA_dispatch.c:17-27 and :31-56), f32 and float16_t element builds."""
+    pkg = os.path.dirname(ita._lib.LIB_PATH)
+    for name, size in (("libita_dispatch_shim.so", 4), ("libita_dispatch_shim_f16.so", 2)):
+        lib = ctypes.CDLL(os.path.join(pkg, name))
+        for sym in ("ITASelfAttention_workgroup", "ITASelfAttention_workgroup_expanded", "ita_dispatch_bind", "ita_dispatch_last_status"):
+            assert hasattr(lib, sym), (name, sym)
+        assert lib.ita_dispatch_elem_size() == size
+        # unbound: the call must not crash, reports an error status
+        buf_in = (ctypes.c_float * 16)()
+        buf_out = (ctypes.c_float * 16)()
+        lib.ITASelfAttention_workgroup(buf_in, buf_out)
+        assert lib.ita_dispatch_last_status() != 0
+        assert lib.ita_dispatch_bind(None, ctypes.c_float(1.0), ctypes.c_float(1.0), 128, 64) != 0

@@ -502,3 +502,38 @@ def test_multi_head_full_config3_sample(ita, R, RC):
         eng.sync_check()
         _cmp(y, RC.mha(p, X, intermediates=False)["Y"], f"config 3 sample softmax={sm}")
         eng.close()
+
+
+# ----------------------------------------------------------------------------------------------------- IREE dispatch symbol
+@pytest.mark.parametrize("f16", [False, True])
+def test_dispatch_shim_computes_the_operator(ita, f16):
+    """``ITASelfAttention_workgroup(in, out)`` (reference plugin/ITA_dispatch.c:17-27; expanded-memref form :31-56) backed by
+    libita_b200: host [1,128,E] buffers in, the module's forward out -- equal to ``ITASelfAttention.forward`` on the same
+    tokens (bit-exact for f32 elements; for float16_t elements equal to the f32 result computed from the f16-rounded input
+    and rounded to f16)."""
+    import ctypes as C
+    q = np.load(os.path.join(GOLDEN, "qat_model_E64.npz"))
+    p = ita.params_from_captured_block(q, "b0_")
+    eng = ita.ITAEngine(p, _dev())
+    s_in, s_out = float(q["b0_s_x"]), float(q["b0_out_proj_sout"])
+    pkg = os.path.dirname(ita._lib.LIB_PATH)
+    shim = C.CDLL(os.path.join(pkg, "libita_dispatch_shim_f16.so" if f16 else "libita_dispatch_shim.so"))
+    shim.ita_dispatch_bind.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_int32, C.c_int32]
+    assert shim.ita_dispatch_bind(eng._h, s_in, s_out, 128, 64) == 0
+    x32 = np.ascontiguousarray(q["attn_in"][1])                      # [128, 64] f32
+    dt = np.float16 if f16 else np.float32
+    x = x32.astype(dt)
+    want = ita.dequantize(eng.forward(ita.quantize(torch.from_numpy(x.astype(np.float32)[None]).to(_dev()), s_in)), s_out)
+    want = want.cpu().numpy()[0].astype(dt)
+    if not f16:
+        assert np.array_equal(want, q["attn_out"][1])               # and that is the reference's captured block output
+    out = np.full_like(x, 7)
+    shim.ITASelfAttention_workgroup.argtypes = [C.c_void_p, C.c_void_p]
+    shim.ITASelfAttention_workgroup(x.ctypes.data, out.ctypes.data)
+    assert shim.ita_dispatch_last_status() == 0
+    assert np.array_equal(out, want)
+    out2 = np.full_like(x, 9)
+    shim.ITASelfAttention_workgroup_expanded.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t] * 2
+    shim.ITASelfAttention_workgroup_expanded(x.ctypes.data, x.ctypes.data, 0, x.size, 1, out2.ctypes.data, out2.ctypes.data, 0, out2.size, 1)
+    assert shim.ita_dispatch_last_status() == 0 and np.array_equal(out2, want)
+    eng.close()
