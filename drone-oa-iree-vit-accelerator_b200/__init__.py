@@ -18,8 +18,9 @@ from .params import (ITAQuantParams, calculate_hw_params, dequantize_bias_to_int
 from .engine import ITAEngine, dequantize, microbench, quantize, residual_layernorm, selftest
 from .attention import ITASelfAttention
 from .golden import Transformer
+from .model import ITAViTLSTM, layer_quant_params
 from .sharding import all_shards, gather_frames, max_over_ranks, shard_range
 
-__all__ = ["ITASelfAttention", "Transformer", "ITAEngine", "ITAQuantParams", "ITAError", "calculate_hw_params",
+__all__ = ["ITASelfAttention", "ITAViTLSTM", "Transformer", "ITAEngine", "ITAQuantParams", "ITAError", "calculate_hw_params",
            "dequantize_bias_to_int32", "translate_torch_scales_to_hw_params", "quantize", "dequantize", "selftest",
            "microbench"]

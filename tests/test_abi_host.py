@@ -166,3 +166,71 @@ def test_dispatch_shim_exports_reference_symbols(ita):
         lib.ITASelfAttention_workgroup(buf_in, buf_out)
         assert lib.ita_dispatch_last_status() != 0
         assert lib.ita_dispatch_bind(None, ctypes.c_float(1.0), ctypes.c_float(1.0), 128, 64) != 0
+
+
+def _same_params(a, b):
+    for k in ("Wq", "Wk", "Wv", "Wo", "Bq", "Bk", "Bv", "Bo", "mult", "shift", "add", "eff"):
+        assert np.array_equal(getattr(a, k), getattr(b, k)), k
+
+
+def test_module_state_dict_round_trip_and_reference_checkpoint(ita):
+    """``state_dict()`` carries every scale / zero-point / weight (round trip), and ``load_state_dict`` accepts the keys of
+    a CONVERTED REFERENCE checkpoint (``attention_blocks.N.q_proj._packed_params._packed_params``, ``.scale``,
+    ``.zero_point``, ``matmul1.scale`` ..., loaded strict=False at tests/export_and_validation_W_B.py:387-392)."""
+    q = np.load(os.path.join(GOLDEN, "qat_model_E64.npz"))
+    want = ita.params_from_captured_block(q, "b0_")
+    sd_ref = torch.load(os.path.join(GOLDEN, "qat_state_E64.pt"), weights_only=False)
+    sub = {k[len("attention_blocks.0."):]: v for k, v in sd_ref.items() if k.startswith("attention_blocks.0.")}
+    m = ita.ITASelfAttention(64, 192, 1)
+    res = m.load_state_dict(sub, strict=False)
+    assert not res.unexpected_keys, res.unexpected_keys
+    _same_params(m.quant_params(128), want)
+    # round trip through our own state dict
+    sd = m.state_dict()
+    for k in ("q_proj.scale", "q_proj.zero_point", "q_proj.weight_scale", "q_proj.weight_int8", "matmul1.scale", "quant.scale"):
+        assert k in sd, k
+    m2 = ita.ITASelfAttention(64, 192, 1)
+    m2.load_state_dict(sd)
+    _same_params(m2.quant_params(128), want)
+    # a parameter change invalidates cached engines (the cache key follows the buffers)
+    v0 = m2._params_version()
+    m2.quant.scale = 0.5
+    assert m2._params_version() != v0
+    m2.q_proj.weight_int8.add_(1)
+    assert m2._params_version() != v0
+    # non-zero zero-points are refused, not silently ignored
+    m2.matmul1.zero_point = 3
+    with pytest.raises(ValueError):
+        m2.quant_params(128)
+
+
+def test_full_model_state_dict_reader_and_float_stages(ita):
+    """``ITAViTLSTM.from_state_dict`` on a converted reference checkpoint: the int8 layer parameters equal the harness'
+    recipe on the captured block, and the float pre/post stages (tokenizer; fusion, decoder, LSTM, head) reproduce the
+    reference's captured tensors (CPU float ops, exact)."""
+    import importlib
+    import sys
+    sys.path.insert(0, GOLDEN)
+    import seeded
+    M = importlib.import_module("drone-oa-iree-vit-accelerator_b200.model")
+    q = np.load(os.path.join(GOLDEN, "qat_model_E64.npz"))
+    sd = dict(torch.load(os.path.join(GOLDEN, "qat_state_E64.pt"), weights_only=False))
+    p, sc = M.layer_quant_params(sd, 0)
+    want = ita.params_from_captured_block(q, "b0_", with_ffn=True)
+    _same_params(p, want)
+    for k in ("Wff", "Wff2", "Bff", "Bff2"):
+        assert np.array_equal(getattr(p, k), getattr(want, k)), k
+    assert sc == {"s_attn_in": float(q["b0_s_x"]), "s_attn_out": float(q["b0_out_proj_sout"]), "s_ffn_in": float(q["b0_fc1_sin"]),
+                  "s_ffn_out": float(q["b0_fc2_sout"])}
+    with pytest.raises(KeyError):
+        M.ITAViTLSTM.from_state_dict(sd)                 # float tensors missing
+    for name, shape in M.reference_float_shapes(1, 64).items():
+        sd[name] = torch.from_numpy(seeded.float_param(name, shape))
+    m = M.ITAViTLSTM.from_state_dict(sd)
+    with torch.no_grad():
+        tok = m.tokens(torch.from_numpy(q["img"]))
+        assert torch.equal(tok, torch.from_numpy(q["tokenizer_out"]))
+        out, (h, c) = m.head(torch.from_numpy(q["norm2_out"]), torch.from_numpy(q["vel"]), torch.from_numpy(q["quat"]))
+        assert np.abs(out.numpy() - q["out"]).max() <= 1e-6 and np.abs(h.numpy() - q["hn"]).max() <= 1e-6
+    with pytest.raises(ValueError):
+        m([torch.zeros(1, 1, 60, 90), torch.zeros(1, 1), torch.zeros(1, 4)])     # CPU tensors: no CPU fallback
