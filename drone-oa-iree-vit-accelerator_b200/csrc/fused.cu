@@ -274,13 +274,13 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   const size_t wbytes = (size_t)3 * WA + WO + kConstBytes;
   std::vector<int8_t> host(wbytes, 0);
   const bool fpm = rqm_offset(mode);
-  // stage index (Q K V QK AV O) of the three concatenated projections Q | V | K
-  const int cat_stage[3] = {0, 2, 1};
-  // [Wq | Wv | Wk]^T as ONE matrix [N = 3P rows, K = E + 32 cols] (the kernel's projection chunks are 128 consecutive rows of
+  // stage index (Q K V QK AV O) of the three concatenated projections Q | K | V
+  const int cat_stage[3] = {0, 1, 2};
+  // [Wq | Wk | Wv]^T as ONE matrix [N = 3P rows, K = E + 32 cols] (the kernel's projection chunks are 128 consecutive rows of
   // it): row n = t*P + j holds column j of W_t (golden layout W [E,P]), then the digits of that column's bias (RQM_FP:
   // bias + the stage's offset, unsigned)
-  const int8_t *Ws[3] = {d->Wq, d->Wv, d->Wk};
-  const int32_t *Bs[3] = {d->Bq, d->Bv, d->Bk};
+  const int8_t *Ws[3] = {d->Wq, d->Wk, d->Wv};
+  const int32_t *Bs[3] = {d->Bq, d->Bk, d->Bv};
   bool digits_ok = true;
   std::vector<int8_t> dig((size_t)(3 * P > E ? 3 * P : E) * kBiasKO, 0);
   for (int t = 0; t < 3; ++t)
@@ -431,6 +431,7 @@ int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, cons
   if (rc) return rc;
   FusedParams prm{};
   prm.wpanels = pl->wpanels;
+  prm.x = x;
   prm.y = y;
   prm.batch = B;
   prm.abort_flag = h->abort_flag;

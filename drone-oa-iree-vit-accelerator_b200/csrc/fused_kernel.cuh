@@ -75,7 +75,7 @@ __host__ __device__ constexpr bool rqm_torch_fp(int mode) { return mode == RQM_T
 __host__ __device__ constexpr int rqm_qk_steps(int mode) { return mode == RQM_TORCH_FP2 ? 3 : 2; }   // offset digit K steps of Q.K^T
 enum { STG_Q = 0, STG_K, STG_V, STG_S, STG_AV, STG_O };
 // per-slot mbarriers
-enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2 /* + region */, BAR_EMPTY = 4 /* + region */, BAR_DEP = 6 /* +STG_Q, STG_K, STG_V, STG_S, STG_AV */, BAR_TURN = 11 };
+enum { BAR_X = 0, BAR_XFREE = 1, BAR_FULL = 2 /* + region */, BAR_EMPTY = 4 /* + region */, BAR_CHUNK = 6 /* + position: its epilogue has written its operand buffer */, BAR_TURN = 15 };
 enum { CK_PROJ = 0, CK_S, CK_AV, CK_O };   // chunk kinds
 
 // Per-stage uniform requant parameters as the fused kernel consumes them.
@@ -96,6 +96,7 @@ struct FRq {
 
 struct FusedParams {
   const int8_t *wpanels;     // device: [Wq^T | Wk^T | Wv^T | Wo^T] (each with its bias-digit K columns) | constant A tile
+  const int8_t *x;           // the input frames (the tiles are loaded through the tensor map; this is for the L2 prefetch)
   int8_t *y;
   long long batch;
   int *abort_flag;
@@ -111,17 +112,24 @@ struct FusedParams {
 template <int E, int P>
 struct Cfg {
   static constexpr int S = kS;
-  static constexpr int PW = 3 * P;                                       // concatenated projection output: Q | V | K
-  static constexpr int NPC = (PW + 127) / 128;                           // projection chunks (128 columns, the last may be 64)
-  static constexpr int NAVC = (P + 127) / 128;                           // A.V chunks
+  static constexpr int PW = 3 * P;                                       // concatenated projection output: Q | K | V
+  static constexpr int NQK = 2 * P / 128;                                // projection chunks with Q and K columns (P % 64 == 0)
+  static constexpr int NVC = (P + 127) / 128;                            // projection chunks with V columns (the last may be 64 wide)
+  static constexpr int NPC = NQK + NVC;                                  // projection chunks
+  static constexpr int NAVC = NVC;                                       // A.V chunks
   static constexpr int NCH = NPC + NAVC + 2;                             // + logits + output projection
-  static constexpr int C_S = NPC, C_AV0 = NPC + 1, C_O = NPC + 1 + NAVC;
+  // Schedule ("position" = order of MMA issue = order of the epilogue = order in the accumulator ring):
+  //     QK[0..NQK)  V[0]  S  V[1..NVC)  AV[0..NAVC)  O
+  // The first V chunk is issued BEFORE the logits and drained while the logits MMA runs; the remaining V chunk (P = 192)
+  // runs on the tensor pipe during ITAmax and is drained while A.V[0] runs (which needs V[0] only).
+  static constexpr int C_S = NQK + 1, C_AV0 = C_S + NVC, C_O = C_AV0 + NAVC;
+  static constexpr int C_LASTPROJ = NVC > 1 ? C_AV0 - 1 : NQK;           // the last reader of the X tile
 #ifdef ITA_C_TURN
   static constexpr int C_TURN = ITA_C_TURN;                              // tuning builds
 #else
-  static constexpr int C_TURN = NPC >= 3 ? 2 : NPC - 1;                  // chunk whose issue lets the other slot start its frame
+  static constexpr int C_TURN = NQK < 2 ? NQK : 2;                       // chunk whose issue lets the other slot start its frame
 #endif
-  static constexpr int WP_BYTES = PW * (E + kBiasK);                     // [Wq | Wv | Wk]^T with bias digits
+  static constexpr int WP_BYTES = PW * (E + kBiasK);                     // [Wq | Wk | Wv]^T with bias digits
   static constexpr int WO_BYTES = E * (P + kBiasKO);                     // Wo^T with bias digits
   static constexpr int OFF_W = 0;
   static constexpr int OFF_WO = WP_BYTES;
@@ -130,12 +138,14 @@ struct Cfg {
   static constexpr int X_BYTES = S * E;
   static constexpr int SP_BYTES = S * P;
   static constexpr int KA_BYTES = (S * P > S * S) ? S * P : S * S;       // K, later the softmax output
-  // the next frame's X tile lives in the part of the K buffer that the softmax output does not cover, when it fits and
-  // only the last projection chunk writes K columns there (that chunk's epilogue runs after the last MMA that reads X)
-  static constexpr bool X_IN_KTAIL = (S * S + X_BYTES <= KA_BYTES) && (2 * P + S >= 128 * (NPC - 1));
+  // The X tile lives in the columns of the V buffer that the LAST V chunk writes (its epilogue runs after its own MMA, the
+  // last reader of X), when it fits there; the next frame's tile is loaded once the last A.V MMA has read V.
+  static constexpr int VLAST_COL0 = 128 * (NVC - 1), VLAST_W = P - VLAST_COL0;
+  static constexpr bool X_IN_V = X_BYTES <= S * VLAST_W;
   static constexpr int OFF_Q = 0, OFF_K = SP_BYTES, OFF_V = OFF_K + KA_BYTES;
-  static constexpr int OFF_X = X_IN_KTAIL ? OFF_K + S * S : OFF_V + SP_BYTES;
-  static constexpr int SLOT_BYTES = OFF_V + SP_BYTES + (X_IN_KTAIL ? 0 : X_BYTES);
+  static constexpr int OFF_X = X_IN_V ? OFF_V + S * VLAST_COL0 : OFF_V + SP_BYTES;
+  static constexpr int C_XFREE = X_IN_V ? C_O - 1 : C_LASTPROJ;          // chunk whose completion frees the X buffer
+  static constexpr int SLOT_BYTES = OFF_V + SP_BYTES + (X_IN_V ? 0 : X_BYTES);
   static constexpr int OFF_SLOT = ((WPANEL_BYTES + 127) / 128) * 128;
   // frames in flight per SM: two when weights + 2 x operand buffers fit the 227 KB, else one (E = 128 with P = 192)
   static constexpr int smem_for(int slots) { return OFF_SLOT + slots * SLOT_BYTES + slots * 2 * S * 8 + 512; }
@@ -150,36 +160,40 @@ struct Cfg {
   static_assert(SMEM_BYTES <= kSmemLimit, "shape does not fit shared memory even with one frame in flight");
   static_assert(E % 64 == 0 && E <= 128 && P % 64 == 0, "E in {64, 128} (one output chunk), P a multiple of 64 (sub-block width)");
   static_assert((1 + kMaxSlots * kBarsPerSlot) * 8 + 8 <= 512, "barrier area");
+  static_assert(BAR_CHUNK + NCH - 1 <= BAR_TURN, "one 'chunk written' barrier per position but the last");
   static_assert(WPANEL_BYTES % 16 == 0 && SLOT_BYTES % 128 == 0, "alignment");
-  // chunk c of a frame -> kind, first column (in the concatenated Q|V|K space for projections), width (128 or 64)
-  static constexpr int kind_of(int c) { return c < NPC ? CK_PROJ : c == C_S ? CK_S : c < C_O ? CK_AV : CK_O; }
-  static constexpr int col0_of(int c) { return kind_of(c) == CK_PROJ ? c * 128 : kind_of(c) == CK_AV ? (c - C_AV0) * 128 : 0; }
+  // position c of a frame -> kind, first column (in the concatenated Q|K|V space for projections), width (128 or 64)
+  static constexpr int kind_of(int c) { return c == C_S ? CK_S : c < C_AV0 ? CK_PROJ : c < C_O ? CK_AV : CK_O; }
+  static constexpr int pidx(int c) { return c < C_S ? c : c - 1; }       // projection chunk number of a CK_PROJ position
+  static constexpr int pos_of_proj(int i) { return i <= NQK ? i : i + 1; }
+  static constexpr int col0_of(int c) { return kind_of(c) == CK_PROJ ? pidx(c) * 128 : kind_of(c) == CK_AV ? (c - C_AV0) * 128 : 0; }
   static constexpr int ncols_of(int c) {
     const int k = kind_of(c);
-    const int left = k == CK_PROJ ? PW - c * 128 : k == CK_AV ? P - (c - C_AV0) * 128 : k == CK_S ? S : E;
+    const int left = k == CK_PROJ ? PW - pidx(c) * 128 : k == CK_AV ? P - (c - C_AV0) * 128 : k == CK_S ? S : E;
     return left < 128 ? left : 128;
   }
   // Both epilogue warpgroups of the slot drain every chunk: warpgroup w takes the sub-block [w * SW, (w + 1) * SW) of the
   // chunk's columns, SW = ncols / 2 (64 or 32).  A sub-block never straddles two stages (P is a multiple of 64).
   static constexpr int sub_w(int c) { return ncols_of(c) / 2; }
-  static constexpr int stage_at(int c, int col) {                        // stage that owns column `col` of chunk c
+  static constexpr int stage_at(int c, int col) {                        // stage that owns column `col` of position c
     const int k = kind_of(c);
     if (k != CK_PROJ) return k == CK_S ? STG_S : k == CK_AV ? STG_AV : STG_O;
-    const int gc = c * 128 + (col < ncols_of(c) ? col : 0);
-    return gc < P ? STG_Q : gc < 2 * P ? STG_V : STG_K;
+    const int gc = pidx(c) * 128 + (col < ncols_of(c) ? col : 0);
+    return gc < P ? STG_Q : gc < 2 * P ? STG_K : STG_V;
   }
   static constexpr int stage_of(int c, int w) { return stage_at(c, w * sub_w(c)); }
   static constexpr int stage_col0(int c, int w) {                        // first column of the sub-block inside its stage's matrix
     const int gc = col0_of(c) + w * sub_w(c);
     return kind_of(c) == CK_PROJ ? gc % P : gc;
   }
-  // arrivals (warps) that complete a stage's "operand written" barrier
-  static constexpr int dep_count(int stage) {
-    int n = 0;
-    for (int c = 0; c < NCH; ++c)
-      for (int w = 0; w < 2; ++w) n += stage_of(c, w) == stage ? 4 : 0;
-    return n;
-  }
+  // Operand dependencies of the MMA K steps, as the LAST position whose epilogue must have written its buffer (epilogues run
+  // in position order, so one "chunk written" barrier per position orders everything before it as well):
+  //   logits K step k (32 of the P columns of Q and K): the projection chunk holding K[:, 32k..]
+  //   A.V chunk j: the logits (ITAmax output) and the V chunk with the same columns
+  //   output projection K step k (32 context columns): the A.V chunk holding them
+  static constexpr int dep_S(int k) { return pos_of_proj((P + 32 * k) / 128); }
+  static constexpr int dep_AV(int j) { return j == 0 ? C_S : C_S + j; }
+  static constexpr int dep_O(int k) { return C_AV0 + (32 * k) / 128; }
 };
 
 // ------------------------------------------------------------------------------- requantisation on the FMA pipe (RQM_FP)
@@ -891,7 +905,7 @@ __device__ __forceinline__ void epilogue_loop(const FusedParams &prm, const Slot
       if constexpr (kind != CK_O) {
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) mbar_arrive(sc.bars + BAR_DEP + stage);
+        if (lane == 0) mbar_arrive(sc.bars + BAR_CHUNK + c);
       }
       ITA_TR(prm, threadIdx.x >> 5, it, c, 3);
     });
@@ -929,7 +943,7 @@ __global__ void __launch_bounds__((Cfg<E, P>::THREADS), 1) k_ita_fused(const __g
         mbar_init(b + BAR_FULL + r, 1);
         mbar_init(b + BAR_EMPTY + r, kEpiWarpsPerSlot);
       }
-      for (int st = STG_Q; st <= STG_AV; ++st) mbar_init(b + BAR_DEP + st, C::dep_count(st));
+      for (int c = 0; c + 1 < C::NCH; ++c) mbar_init(b + BAR_CHUNK + c, kEpiWarpsPerSlot);
       mbar_init(b + BAR_TURN, 1);
     }
     fence_mbar_init();
@@ -954,6 +968,9 @@ __global__ void __launch_bounds__((Cfg<E, P>::THREADS), 1) k_ita_fused(const __g
         if (iters[s] > 0)
           load_x_tile<E>(smem + C::OFF_SLOT + s * C::SLOT_BYTES + C::OFF_X, &xmap, (long long)blockIdx.x * kSlots + s,
                          slot_bars + s * kBarsPerSlot + BAR_X);
+        // the tile after that goes to L2 now: its shared-memory buffer is freed late in the frame (C_XFREE), and the load
+        // that follows should not have to go to HBM
+        if (iters[s] > 1) l2_prefetch(prm.x + ((long long)blockIdx.x * kSlots + s + frame_stride) * (kS * E), kS * E);
       }
       bool ok = true;
       for (long long it = 0; it + 1 < mx && ok; ++it)
@@ -964,6 +981,7 @@ __global__ void __launch_bounds__((Cfg<E, P>::THREADS), 1) k_ita_fused(const __g
             if (ok)
               load_x_tile<E>(smem + C::OFF_SLOT + s * C::SLOT_BYTES + C::OFF_X, &xmap,
                              (long long)blockIdx.x * kSlots + s + (it + 1) * frame_stride, slot_bars + s * kBarsPerSlot + BAR_X);
+            if (ok && it + 2 < iters[s]) l2_prefetch(prm.x + ((long long)blockIdx.x * kSlots + s + (it + 2) * frame_stride) * (kS * E), kS * E);
           }
     }
     __syncwarp();
@@ -985,6 +1003,7 @@ __global__ void __launch_bounds__((Cfg<E, P>::THREADS), 1) k_ita_fused(const __g
                      v16 = slot16 + (C::OFF_V >> 4);
       const uint32_t d_base = tmem_base + slot * kTmemColsPerSlot;
       uint32_t n = 0;                                 // running chunk number: region n & 1, its (n >> 1)-th use
+      int written = 0;                                // positions of the current frame whose 'chunk written' barrier has been passed
       for (long long it = 0; it < iters && ok; ++it) {
         const uint32_t ph = (uint32_t)(it & 1);
         static_for<0, C::NCH>([&](auto cc) {
@@ -1031,56 +1050,80 @@ __global__ void __launch_bounds__((Cfg<E, P>::THREADS), 1) k_ita_fused(const __g
             }
           }
           __syncwarp();
-          if constexpr (c == 0) ok = ok && mbar_wait(b + BAR_X, ph, prm.abort_flag);
-          if constexpr (c == C::C_S) ok = ok && mbar_wait(b + BAR_DEP + STG_Q, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_K, ph, prm.abort_flag);
-          if constexpr (c == C::C_AV0) ok = ok && mbar_wait(b + BAR_DEP + STG_V, ph, prm.abort_flag) && mbar_wait(b + BAR_DEP + STG_S, ph, prm.abort_flag);
-          if constexpr (c == C::C_O) ok = ok && mbar_wait(b + BAR_DEP + STG_AV, ph, prm.abort_flag);
+          if constexpr (c == 0) {
+            ok = ok && mbar_wait(b + BAR_X, ph, prm.abort_flag);
+            written = 0;
+          }
           if (!ok) return;
           tc_fence_after();
           ITA_TR(prm, warp, it, c, 2);
           const uint32_t d_tmem = d_base + r * kRegionCols;
-          if (leader) {
+          // wait until the epilogue of position `pos` (and so of every position before it) has written its operand buffer
+          auto need = [&](int pos) {
+            while (ok && written <= pos) {
+              ok = mbar_wait(b + BAR_CHUNK + written, ph, prm.abort_flag);
+              ++written;
+              tc_fence_after();
+            }
+            return ok;
+          };
+          {
             if constexpr (kind == CK_PROJ) {
-              // projections: A = X [S rows, K = E] K-major; B = rows [col0, +NC) of [Wq | Wv | Wk]^T [3P rows, K = E + 32]
+              // projections: A = X [S rows, K = E] K-major; B = rows [col0, +NC) of [Wq | Wk | Wv]^T [3P rows, K = E + 32]
               // K-major; the last K step multiplies the constant tile with the bias (+ offset) digits
               constexpr uint32_t ID = make_idesc_i8(kS, NC, 1, 1, 0, 0), IDD = make_idesc_i8(kS, NC, DSG, DSG, 0, 0);
               constexpr uint32_t wt = col0 * 16;
+              if (leader) {
 #pragma unroll
-              for (int k = 0; k < E / 32; ++k)
-                umma_i8(d_tmem, make_smem_desc_rel(x16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(w16, wt + k * 2 * C::PW * 16, C::PW * 16, 128), ID, k > 0);
-              umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, wt + (E / 16) * C::PW * 16, C::PW * 16, 128),
-                      IDD, 1);
+                for (int k = 0; k < E / 32; ++k)
+                  umma_i8(d_tmem, make_smem_desc_rel(x16, k * 2 * kS * 16, kS * 16, 128),
+                          make_smem_desc_rel(w16, wt + k * 2 * C::PW * 16, C::PW * 16, 128), ID, k > 0);
+                umma_i8(d_tmem, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, wt + (E / 16) * C::PW * 16, C::PW * 16, 128),
+                        IDD, 1);
+              }
             } else if constexpr (kind == CK_S) {
-              // logits: A = Q [S, K = P] K-major; B = K [S rows (keys), K = P] K-major (RQM_FP: on top of the two offset steps)
+              // logits: A = Q [S, K = P] K-major; B = K [S rows (keys), K = P] K-major (RQM_FP: on top of the offset steps).
+              // A K step is issued as soon as the projection chunk with its K columns is written (Q comes before K).
               constexpr uint32_t ID = make_idesc_i8(kS, kS, 1, 1, 0, 0);
-#pragma unroll
-              for (int k = 0; k < P / 32; ++k)
-                umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128), ID, (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
+              static_for<0, P / 32>([&](auto kk) {
+                constexpr int k = decltype(kk)::value;
+                if (!need(C::dep_S(k))) return;
+                if (leader)
+                  umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128),
+                          make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128), ID, (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
+              });
             } else if constexpr (kind == CK_AV) {
               // context: A = Asm [S, K = S] u8 K-major (in the K buffer); B = columns [col0, +NC) of V [K = S rows, N = P]
               // MN-major (RQM_FP: on top of the offset step)
               constexpr uint32_t ID = make_idesc_i8(kS, NC, 0, 1, 0, 1);
+              if (need(C::dep_AV(c - C::C_AV0)) && leader) {
 #pragma unroll
-              for (int k = 0; k < kS / 32; ++k)
-                umma_i8(d_tmem, make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128),
-                        make_smem_desc_rel(v16, (col0 / 16) * kS * 16 + k * 32 * 16, 128, kS * 16), ID, (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
+                for (int k = 0; k < kS / 32; ++k)
+                  umma_i8(d_tmem, make_smem_desc_rel(k16, k * 2 * kS * 16, kS * 16, 128),
+                          make_smem_desc_rel(v16, (col0 / 16) * kS * 16 + k * 32 * 16, 128, kS * 16), ID, (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
+              }
             } else {
               // output projection: A = O [S, K = P] K-major (in the Q buffer); B = Wo^T [E rows, K = P + 64], on top of the
-              // digit steps issued above (one for the integer forms, two for RQM_FP)
+              // digit steps issued above (one for the integer forms, two for RQM_FP); a K step goes out as soon as the A.V
+              // chunk with its context columns is written
               constexpr uint32_t ID = make_idesc_i8(kS, E, 1, 1, 0, 0);
               constexpr uint32_t wo = C::OFF_WO;
-#pragma unroll
-              for (int k = 0; k < P / 32; ++k)
-                umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128), make_smem_desc_rel(w16, wo + k * 2 * E * 16, E * 16, 128),
-                        ID, 1);
+              static_for<0, P / 32>([&](auto kk) {
+                constexpr int k = decltype(kk)::value;
+                if (!need(C::dep_O(k))) return;
+                if (leader)
+                  umma_i8(d_tmem, make_smem_desc_rel(q16, k * 2 * kS * 16, kS * 16, 128), make_smem_desc_rel(w16, wo + k * 2 * E * 16, E * 16, 128),
+                          ID, 1);
+              });
             }
+          }
+          if (!ok) return;
+          if (leader) {
             umma_commit(b + BAR_FULL + r);
             if constexpr (c == C::C_TURN) mbar_arrive(b + BAR_TURN);
             // the X buffer may be overwritten once its last reader is complete: the last projection, or -- when X shares
             // storage with the K columns beyond the softmax output -- the logits MMA
-            if constexpr (C::X_IN_KTAIL ? (c == C::C_S) : (c == C::NPC - 1)) umma_commit(b + BAR_XFREE);
+            if constexpr (c == C::C_XFREE) umma_commit(b + BAR_XFREE);
           }
           __syncwarp();
           ITA_TR(prm, warp, it, c, 3);

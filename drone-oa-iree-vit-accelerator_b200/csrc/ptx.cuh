@@ -41,7 +41,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
 // Bounded wait.  The loop itself is four instructions (try_wait suspends the thread in hardware for a while when the
 // phase is not complete); it gives up after kWaitSpinLimit failed polls and raises `*abort_flag` (a device int the host
 // checks after the launch), so that a protocol bug shows up as an error code instead of a hung GPU.
-constexpr uint32_t kWaitSpinLimit = 1u << 24;
+constexpr uint32_t kWaitSpinLimit = 1u << 22;   // rounds of four polls
 #ifdef ITA_OLD_WAIT
 __device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *abort_flag) {
   if (mbar_try_wait(bar, parity)) return true;
@@ -76,6 +76,16 @@ __device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity, int *a
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
 #endif
       "@p bra ITA_DONE_%=;\n\t"
+#ifndef ITA_WAIT_NO_UNROLL
+      // three more polls before the poll counter is touched: the counter's add + compare run on the ALU pipe, which is the
+      // busiest pipe of the fused kernels, and waiting warps spin next to working ones
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "@p bra ITA_DONE_%=;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "@p bra ITA_DONE_%=;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "@p bra ITA_DONE_%=;\n\t"
+#endif
       "add.u32 n, n, 1;\n\t"
       "setp.lt.u32 q, n, %3;\n\t"
       "@q bra ITA_WAIT_%=;\n"
@@ -126,6 +136,10 @@ __device__ __forceinline__ void tma_load_2d(void *dst_smem, const CUtensorMap *m
           smem_u32(dst_smem)),
       "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
       : "memory");
+}
+// ask for a contiguous global range to be brought into L2 (no completion tracking; bytes a multiple of 16, 16 B aligned)
+__device__ __forceinline__ void l2_prefetch(const void *src_gmem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(src_gmem), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
   asm volatile("prefetch.tensormap [%0];\n" ::"l"(map) : "memory");

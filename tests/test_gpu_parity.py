@@ -445,15 +445,15 @@ def test_module_surface(ita, R):
         lin.weight_scale = float(q[pre + name + "_sw"])
         lin.scale = float(q[pre + name + "_sout"])
         s_in = float(q[pre + name + "_sin"])
-        lin.bias.copy_(torch.from_numpy(q[pre + name + "_bias_i32"].astype(np.float64) * s_in * lin.weight_scale).float())
+        lin.bias.copy_(torch.from_numpy(q[pre + name + "_bias_i32"].astype(np.float64) * s_in * float(lin.weight_scale)).float())
     m.quant.scale = float(q[pre + "q_proj_sin"])
     m.matmul1.scale = float(q[pre + "qk_sout"])
     m.matmul2.scale = float(q[pre + "av_sout"])
     xq = q[pre + "x"]
-    x = torch.from_numpy(xq.astype(np.float32) * np.float32(m.quant.scale)).to(_dev())
+    x = torch.from_numpy(xq.astype(np.float32) * np.float32(float(m.quant.scale))).to(_dev())
     y = m(x)
     assert y.dtype == torch.float32 and tuple(y.shape) == tuple(x.shape)
-    want = q[pre + "out_proj_out"].reshape(xq.shape).astype(np.float32) * np.float32(m.out_proj.scale)
+    want = q[pre + "out_proj_out"].reshape(xq.shape).astype(np.float32) * np.float32(float(m.out_proj.scale))
     assert np.array_equal(y.cpu().numpy(), want)
     yq = m.forward_int8(torch.from_numpy(xq).to(_dev()))
     _cmp(yq, q[pre + "out_proj_out"], "module forward_int8 vs fixture")
@@ -465,6 +465,65 @@ def test_module_surface(ita, R):
     s = 0.5
     v = torch.tensor([0.25, 0.75, -0.25, -0.75, 1.25, 1000.0, -1000.0, 0.0], device=_dev())
     assert ita.quantize(v, s).cpu().tolist() == [0, 2, 0, -2, 2, 127, -128, 0]
+
+
+def test_module_hooks_fire_with_quantised_stage_tensors(ita, R):
+    """Forward hooks on the named submodules (the way tests/export_and_validation_W_B.py:186-205 captures a block) receive
+    quantised tensors with the reference's shapes, scales and integer values; registering hooks does not change the output."""
+    q = np.load(os.path.join(GOLDEN, "qat_model_E64.npz"))
+    sd_ref = torch.load(os.path.join(GOLDEN, "qat_state_E64.pt"), weights_only=False)
+    sub = {k[len("attention_blocks.0."):]: v for k, v in sd_ref.items() if k.startswith("attention_blocks.0.")}
+    m = ita.ITASelfAttention(64, 192, 1)
+    m.load_state_dict(sub, strict=False)
+    x = torch.from_numpy(q["attn_in"]).to(_dev())
+    y_plain = m(x)
+    got = {}
+    handles = [getattr(m, n).register_forward_hook(lambda mod, i, o, n=n: got.__setitem__(n, o))
+               for n in ("quant", "q_proj", "k_proj", "v_proj", "matmul1", "custom_softmax", "matmul2", "out_proj", "dequant")]
+    y_hook = m(x)
+    for h in handles:
+        h.remove()
+    assert torch.equal(y_plain, y_hook)
+    assert np.array_equal(y_plain.cpu().numpy(), q["attn_out"])
+    want = {"quant": "b0_x", "q_proj": "b0_q_proj_out", "k_proj": "b0_k_proj_out", "v_proj": "b0_v_proj_out", "matmul1": "b0_qk_out",
+            "custom_softmax": "b0_softmax_out", "matmul2": "b0_av_out", "out_proj": "b0_out_proj_out"}
+    for name, key in want.items():
+        t = got[name]
+        assert t.is_quantized and tuple(t.shape) == tuple(q[key].shape), (name, tuple(t.shape), q[key].shape)
+        assert np.array_equal(t.int_repr().numpy(), q[key]), name
+    assert abs(got["q_proj"].q_scale() - float(q["b0_q_proj_sout"])) <= 1e-12 * float(q["b0_q_proj_sout"]) + 1e-15
+    assert got["custom_softmax"].dtype == torch.quint8 and got["matmul1"].dtype == torch.qint8
+    assert np.array_equal(got["dequant"].numpy(), q["attn_out"])
+    assert not m._has_hooks()
+
+
+def test_full_model_forward_vs_reference_trace(ita, R):
+    """``ITAViTLSTM.forward`` ([img, velocity, quaternion] -> command, LSTM state; reference QAT/model.py:88-133) built from
+    the converted reference checkpoint, against the trace of the reference model on the same inputs
+    (tests/golden/make_golden.py --new).  Float stages run in torch on the GPU, the encoder layer in libita_b200.
+    Tolerances: tokens 1e-5 (cuDNN conv vs the CPU conv of the trace); encoder output like test_encoder_layer (a token within
+    float noise of a rounding boundary may quantise one LSB apart); command and LSTM state 5e-3 absolute."""
+    import importlib
+    import seeded
+    M = importlib.import_module("drone-oa-iree-vit-accelerator_b200.model")
+    q = np.load(os.path.join(GOLDEN, "qat_model_E64.npz"))
+    sd = dict(torch.load(os.path.join(GOLDEN, "qat_state_E64.pt"), weights_only=False))
+    for name, shape in M.reference_float_shapes(1, 64).items():
+        sd[name] = torch.from_numpy(seeded.float_param(name, shape))
+    m = M.ITAViTLSTM.from_state_dict(sd).to(_dev())
+    dev = lambda k: torch.from_numpy(q[k]).to(_dev())
+    tok = m.tokens(dev("img"))
+    assert np.abs(tok.cpu().numpy() - q["tokenizer_out"]).max() <= 1e-5
+    enc = m.encode(dev("tokenizer_out")).cpu().numpy()
+    d = np.abs(enc - q["norm2_out"])
+    assert (d > 1e-4).mean() <= 0.01 and d.max() <= 0.25, ((d > 1e-4).mean(), d.max())
+    out, (hn, cn) = m([dev("img"), dev("vel"), dev("quat")])
+    assert tuple(out.shape) == (3, 3) and tuple(hn.shape) == (3, 3, 128)
+    assert np.abs(out.cpu().numpy() - q["out"]).max() <= 5e-3, np.abs(out.cpu().numpy() - q["out"]).max()
+    assert np.abs(hn.cpu().numpy() - q["hn"]).max() <= 5e-3 and np.abs(cn.cpu().numpy() - q["cn"]).max() <= 5e-3
+    # second step: the recurrent state goes back in (the trace's second call flipped the batch)
+    out2, (hn2, _) = m([torch.flip(dev("img"), dims=[0]), dev("vel"), dev("quat"), (hn, cn)])
+    assert np.abs(out2.cpu().numpy() - q["out2"]).max() <= 5e-3 and np.abs(hn2.cpu().numpy() - q["hn2"]).max() <= 5e-3
 
 
 # ----------------------------------------------------------------------------------------------------- full-size properties

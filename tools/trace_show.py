@@ -1,9 +1,9 @@
 """Developer tool: print the per-chunk timeline recorded by tools/trace_run.py (cycles relative to the iteration start)."""
 import sys
 import numpy as np
-t = np.fromfile(sys.argv[1], dtype=np.int64).reshape(19, 9, 32, 4)
+t = np.fromfile(sys.argv[1], dtype=np.int64).reshape(-1, 9, 32, 4)
 NQ = 3
-names = ["P0", "P1", "P2", "P3", "P4", "S", "AV0", "AV1", "O"]
+names = ["QK0", "QK1", "QK2", "V0", "S", "V1", "AV0", "AV1", "O"]   # schedule positions of Cfg<64,192>
 it = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 WG = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 for slot in (0, 1):
