@@ -73,8 +73,8 @@ static int check_abort(ita_mha_handle *h, cudaStream_t s, const char *what) {
 
 static int forward_dev(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, int path, cudaStream_t s) {
   if (path == ITA_PATH_AUTO) {
-    path = h->fused ? ITA_PATH_FUSED : ITA_PATH_STAGED;
-    if (!h->fused && !h->warned_staged) {     // say it once: the staged kernels are the correctness path, not the fast one
+    path = (h->fused || h->mh) ? ITA_PATH_FUSED : ITA_PATH_STAGED;
+    if (!h->fused && !h->mh && !h->warned_staged) {     // say it once: the staged kernels are the correctness path, not the fast one
       h->warned_staged = true;
       fprintf(stderr, "libita_b200: ITA_PATH_AUTO falls back to the staged (CUDA-core) kernels for S=%d E=%d P=%d H=%d: %s\n", h->S, h->E,
               h->P, h->H, h->fused_reason.c_str());
@@ -217,7 +217,7 @@ void ita_mha_destroy(ita_mha_handle *h) {
 
 int ita_mha_fused_supported(const ita_mha_handle *h) {
   if (!h) return 0;
-  if (h->fused) return 1;
+  if (h->fused || h->mh) return 1;
   set_error("%s", h->fused_reason.c_str());
   return 0;
 }
@@ -284,7 +284,7 @@ static int forward_host_impl(ita_mha_handle *h, const int8_t *x_host, int8_t *y_
     const int want = atoi(e);
     if (want >= 1 && want <= ita_mha_handle::kHostChunks && batch >= want) nchunk = want;
   }
-  if (path == ITA_PATH_AUTO) path = h->fused ? ITA_PATH_FUSED : ITA_PATH_STAGED;
+  if (path == ITA_PATH_AUTO) path = (h->fused || h->mh) ? ITA_PATH_FUSED : ITA_PATH_STAGED;
   if (path == ITA_PATH_STAGED) nchunk = 1;   // the staged path shares one scratch area
   const int64_t per = (batch + nchunk - 1) / nchunk;
   if (nchunk > 1 && !h->pipe_ready) {

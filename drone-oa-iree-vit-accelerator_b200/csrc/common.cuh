@@ -50,6 +50,7 @@ __device__ __forceinline__ int32_t requant_general(int32_t acc, const Rq &r) {
 // ---- handle ----------------------------------------------------------------------------------------------------------
 struct FusedPlan;   // fused.cu
 struct FfnPlan;     // ffn.cu
+struct MhPlan;      // mh.cu
 
 }  // namespace ita
 
@@ -75,7 +76,8 @@ struct ita_mha_handle {
   cudaEvent_t ev_in[kHostChunks] = {}, ev_k[kHostChunks] = {}, ev_start = nullptr, ev_done[2] = {nullptr, nullptr};
   bool pipe_ready = false;
   ita::FusedPlan *fused = nullptr;      // non-null when the fused tcgen05 kernel supports this handle
-  std::string fused_reason;             // why not, otherwise
+  ita::MhPlan *mh = nullptr;            // non-null when the multi-head S = 256 tcgen05 kernels support this handle
+  std::string fused_reason;             // why neither, otherwise
   bool warned_staged = false;           // ITA_PATH_AUTO fallback notice printed
   ita::FfnPlan *ffn = nullptr;          // non-null when the fused tcgen05 FFN kernel supports this handle
   std::string ffn_reason;
@@ -95,6 +97,11 @@ int launch_dequantize(const int8_t *q, float *y, int64_t n, float scale, cudaStr
 int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d);   // sets h->fused or h->fused_reason; returns ITA_OK unless CUDA fails
 void fused_plan_destroy(ita_mha_handle *h);
 int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, const ita_mha_stages *dump, cudaStream_t s);
+// mh.cu
+int mh_plan_create(ita_mha_handle *h, const ita_mha_desc *d);      // sets h->mh or h->fused_reason
+void mh_plan_destroy(ita_mha_handle *h);
+int mh_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, const ita_mha_stages *dump, cudaStream_t s);
+std::string describe_mh(const ita_mha_handle *h);
 // ffn.cu
 int ffn_plan_create(ita_mha_handle *h, const ita_mha_desc *d);     // sets h->ffn or h->ffn_reason
 void ffn_plan_destroy(ita_mha_handle *h);

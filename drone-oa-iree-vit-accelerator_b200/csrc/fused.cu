@@ -172,7 +172,8 @@ int fused_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
     h->fused_reason = why;
     return ITA_OK;
   };
-  if (h->S != kS) return no("fused kernel needs S == 128");
+  if (h->S == 256) return mh_plan_create(h, d);      // multi-head kernels (mh.cu)
+  if (h->S != kS) return no("fused kernel needs S == 128 (or S == 256 for the multi-head kernels)");
   if (h->H != 1) return no("fused kernel needs H == 1");
   const int E = h->E, P = h->P;
   const FusedShape *shape = nullptr;
@@ -391,6 +392,7 @@ const char *rqm_name(int mode) { return mode >= 0 && mode <= 5 ? kModeNames[mode
 
 std::string describe_fused(const ita_mha_handle *h) {
   char b[256];
+  if (h->mh) return describe_mh(h);
   if (!h->fused) {
     snprintf(b, sizeof(b), "attention: staged CUDA-core kernels (%s)", h->fused_reason.c_str());
   } else {
@@ -402,6 +404,7 @@ std::string describe_fused(const ita_mha_handle *h) {
 }
 
 void fused_plan_destroy(ita_mha_handle *h) {
+  mh_plan_destroy(h);
   if (h->fused) {
     cudaFree(h->fused->wpanels);
     delete h->fused;
@@ -410,6 +413,7 @@ void fused_plan_destroy(ita_mha_handle *h) {
 }
 
 int fused_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, const ita_mha_stages *dump, cudaStream_t s) {
+  if (h->mh) return mh_forward(h, x, y, B, dump, s);
   FusedPlan *pl = h->fused;
   if (!pl) {
     set_error("fused path unavailable: %s", h->fused_reason.c_str());

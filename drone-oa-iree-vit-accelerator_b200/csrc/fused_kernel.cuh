@@ -422,10 +422,11 @@ __device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
 //   col        first of the 32 columns inside that matrix
 //   grow       global pointer to the first of these 32 columns (natural layout) or nullptr
 //   RELU       max(0, .) on the requantised value (FFN fc1): the sign bytes are replicated into a mask by one PRMT
-template <int MODE, int ALT, bool RELU = false>
-__device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const FRq &r, int8_t *panel, int row, int col, int8_t *grow) {
+//   N          accumulators per call (32 or 16);  PR = rows of the panel buffer (kS, or 256 for the multi-head kernel's Q/K/V)
+template <int MODE, int ALT, bool RELU = false, int N = 32, int PR = kS>
+__device__ __forceinline__ void requant_store32(const uint32_t (&v)[N], const FRq &r, int8_t *panel, int row, int col, int8_t *grow) {
 #pragma unroll
-  for (int j = 0; j < 32; j += 16) {
+  for (int j = 0; j < N; j += 16) {
     uint32_t w[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -453,7 +454,7 @@ __device__ __forceinline__ void requant_store32(const uint32_t (&v)[32], const F
       }
     }
     const uint4 o = make_uint4(w[0], w[1], w[2], w[3]);
-    if (panel) *reinterpret_cast<uint4 *>(panel + ((col + j) >> 4) * (kS * 16) + row * 16) = o;
+    if (panel) *reinterpret_cast<uint4 *>(panel + ((col + j) >> 4) * (PR * 16) + row * 16) = o;
     if (grow) *reinterpret_cast<uint4 *>(grow + j) = o;
   }
 }
@@ -475,7 +476,27 @@ struct PairCtx {
   uint32_t bar_id;     // named barrier shared by the two warps of the pair (64 threads)
   int2 *xch;           // this slot's exchange area [2][kS]
 };
-__device__ __forceinline__ void pair_sync(const PairCtx &pc) { named_bar_sync(pc.bar_id, 64); }
+template <int NPART = 2>
+__device__ __forceinline__ void pair_sync(const PairCtx &pc) { named_bar_sync(pc.bar_id, 32 * NPART); }
+// The NPART threads that share a row (NPART = 2: the pair above; 4: the multi-head kernel, 64 of 256 keys each) publish a
+// partial row max / row sum and combine all of them (own value included) after the barrier.
+template <int NPART>
+__device__ __forceinline__ int xchg_max(const PairCtx &pc, int part, int row, int v) {
+  pc.xch[part * kS + row].x = v;
+  pair_sync<NPART>(pc);
+#pragma unroll
+  for (int p = 0; p < NPART; ++p) v = max(v, pc.xch[p * kS + row].x);
+  return v;
+}
+template <int NPART>
+__device__ __forceinline__ uint32_t xchg_sum(const PairCtx &pc, int part, int row, uint32_t v) {
+  pc.xch[part * kS + row].y = (int)v;
+  pair_sync<NPART>(pc);
+  uint32_t t = 0;
+#pragma unroll
+  for (int p = 0; p < NPART; ++p) t += (uint32_t)pc.xch[p * kS + row].y;
+  return t;
+}
 
 // repo_global (models/ITA/QAT/ITA_softmax.py:51-61): m = row max, d = m - a, n = 256 >> d, inv = floor(255*2^16 / sum n),
 // out = (n * inv) >> 16 == (inv >> 8) >> d.  Requantisation is monotone, so the row max is taken on the raw
@@ -485,11 +506,10 @@ __device__ __forceinline__ void pair_sync(const PairCtx &pc) { named_bar_sync(pc
 // <= 127) and low saturation cannot matter (m >= -119: a saturated element has d > 8 either way); other rows (and
 // the other requant forms) take the general form with the explicit clamp.  The choice is made per warp; both warps of
 // a pair hold the same rows and therefore choose alike.
-template <int MODE, int ALT, bool DUMP, class R>
+template <int MODE, int ALT, bool DUMP, int NPART = 2, class R>
 __device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                  const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
-  int2 *mine = pc.xch + HALF * kS + row, *other = pc.xch + (HALF ^ 1) * kS + row;
   // ---- pass 1: max of the raw accumulators
   int amax = (int)0x80000000;
   tmem_walk<2>(addr,
@@ -498,9 +518,7 @@ __device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq
                  for (int i = 0; i < 32; ++i) amax = max(amax, (int)v[i]);
                },
                NoRelease{});
-  mine->x = amax;
-  pair_sync(pc);
-  amax = max(amax, other->x);
+  amax = xchg_max<NPART>(pc, HALF, row, amax);
   const int m_un = rq_apply<MODE, 0>(amax, rq, 0);
   const int m = min(max(m_un, -128), 127);
   bool fast = false;
@@ -521,9 +539,7 @@ __device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq
                    for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist((int)v[i], i));
                  },
                  NoRelease{});
-    mine->y = (int)sum;
-    pair_sync(pc);
-    sum += (uint32_t)other->y;
+    sum = xchg_sum<NPART>(pc, HALF, row, sum);
     const uint32_t inv8 = ((255u * 65536u) / sum) >> 8;
     tmem_walk<2>(addr,
                  [&](auto gg, const uint32_t(&v)[32]) {
@@ -554,9 +570,7 @@ __device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq
                    for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist((int)v[i]));
                  },
                  NoRelease{});
-    mine->y = (int)sum;
-    pair_sync(pc);
-    sum += (uint32_t)other->y;
+    sum = xchg_sum<NPART>(pc, HALF, row, sum);
     const uint32_t inv8 = ((255u * 65536u) / sum) >> 8;
     tmem_walk<2>(addr,
                  [&](auto gg, const uint32_t(&v)[32]) {
@@ -593,11 +607,10 @@ __device__ __forceinline__ void itamax_repo_half(int HALF, uint32_t t, const FRq
 // The same ITAmax with the requantisation on the FMA pipe (RQM_FP).  TMEM holds bits = INIT + acc (monotone in acc), so
 // pass 1 takes the max of the raw patterns; z = rq_fp_bits(.) is a + 128 before saturation.  Fast rows (no logit
 // saturates high, m >= -119) get the distance d = m - a from one FFMA.RP per element; other rows clamp explicitly.
-template <int MODE, bool DUMP, class R>
+template <int MODE, bool DUMP, int NPART = 2, class R>
 __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                     const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
-  int2 *mine = pc.xch + HALF * kS + row, *other = pc.xch + (HALF ^ 1) * kS + row;
   int amax = 0;                                   // patterns are positive
   tmem_walk<2>(addr,
                [&](auto, const uint32_t(&v)[32]) {
@@ -605,9 +618,7 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
                  for (int i = 0; i < 32; ++i) amax = max(amax, (int)v[i]);
                },
                NoRelease{});
-  mine->x = amax;
-  pair_sync(pc);
-  amax = max(amax, other->x);
+  amax = xchg_max<NPART>(pc, HALF, row, amax);
   const int zmax = rq_off_bits<MODE>((uint32_t)amax, rq);
   const int mp = min(max(zmax, 0), 255);          // m + 128
   bool fast = false;
@@ -684,9 +695,7 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
                    }
                  },
                  NoRelease{});
-    mine->y = (int)sum;
-    pair_sync(pc);
-    sum += (uint32_t)other->y;
+    sum = xchg_sum<NPART>(pc, HALF, row, sum);
     const uint32_t inv8 = ((((255u * 65536u) / sum) >> 8) << 1) << odd;
     tmem_walk<2>(addr,
                  [&](auto gg, const uint32_t(&v)[32]) {
@@ -717,9 +726,7 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
                    for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist(v[i]));
                  },
                  NoRelease{});
-    mine->y = (int)sum;
-    pair_sync(pc);
-    sum += (uint32_t)other->y;
+    sum = xchg_sum<NPART>(pc, HALF, row, sum);
     const uint32_t inv8 = ((255u * 65536u) / sum) >> 8;
     tmem_walk<2>(addr,
                  [&](auto gg, const uint32_t(&v)[32]) {
@@ -753,8 +760,9 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
 
 // Recalled golden-model streaming softmax (the stream16 variant): 16-column groups in
 // column order, running max m and denominator, eps = 1/32 with round-half-up; then out = inv >> rhu((m - a) / 32).
-// The row is walked in column order: HALF 1 continues from the state HALF 0 publishes.
-template <int MODE, bool DUMP, class R>
+// The row is walked in column order: part p continues from the state part p - 1 publishes (NPART - 1 hand-overs, each a
+// named barrier of the NPART warps that share the rows), and everybody reads the final state of the last part.
+template <int MODE, bool DUMP, int NPART = 2, class R>
 __device__ __forceinline__ void itamax_stream_half(int HALF, uint32_t t, const FRq &rq, int8_t *k_buf, int row, int8_t *gA, uint8_t *gAsm,
                                                    const PairCtx &pc, R &&release) {
   auto addr = [&](int g) { return t + (uint32_t)g * 32u; };
@@ -765,43 +773,40 @@ __device__ __forceinline__ void itamax_stream_half(int HALF, uint32_t t, const F
       return (uint32_t)(min(max(rq_apply<MODE, 0>((int)acc, rq, 0), -128), 127) + 128);
     }
   };
-  int2 *st0 = pc.xch + row, *st1 = pc.xch + kS + row;
   uint32_t m = 0, tot = 0;
-  if (HALF == 1) {
-    pair_sync(pc);                 // HALF 0 has published its running state
-    m = (uint32_t)st0->x;
-    tot = (uint32_t)st0->y;
+#pragma unroll
+  for (int turn = 0; turn < NPART; ++turn) {
+    if (HALF == turn) {
+      if (turn > 0) {                // the part before has published its running state
+        m = (uint32_t)pc.xch[(turn - 1) * kS + row].x;
+        tot = (uint32_t)pc.xch[(turn - 1) * kS + row].y;
+      }
+      tmem_walk<2>(addr,
+                   [&](auto, const uint32_t(&v)[32]) {
+#pragma unroll
+                     for (int h = 0; h < 2; ++h) {
+                       uint32_t b[16];
+                       uint32_t cm = 0;
+#pragma unroll
+                       for (int i = 0; i < 16; ++i) {
+                         b[i] = biased(v[h * 16 + i]);
+                         cm = max(cm, b[i]);
+                       }
+                       if (cm > m) {
+                         tot = shr_clamp(tot, (cm - m + 16) >> 5);
+                         m = cm;
+                       }
+#pragma unroll
+                       for (int i = 0; i < 16; ++i) tot += 256u >> ((m - b[i] + 16) >> 5);
+                     }
+                   },
+                   NoRelease{});
+      pc.xch[turn * kS + row] = make_int2((int)m, (int)tot);
+    }
+    pair_sync<NPART>(pc);
   }
-  tmem_walk<2>(addr,
-               [&](auto, const uint32_t(&v)[32]) {
-#pragma unroll
-                 for (int h = 0; h < 2; ++h) {
-                   uint32_t b[16];
-                   uint32_t cm = 0;
-#pragma unroll
-                   for (int i = 0; i < 16; ++i) {
-                     b[i] = biased(v[h * 16 + i]);
-                     cm = max(cm, b[i]);
-                   }
-                   if (cm > m) {
-                     tot = shr_clamp(tot, (cm - m + 16) >> 5);
-                     m = cm;
-                   }
-#pragma unroll
-                   for (int i = 0; i < 16; ++i) tot += 256u >> ((m - b[i] + 16) >> 5);
-                 }
-               },
-               NoRelease{});
-  if (HALF == 0) {
-    *st0 = make_int2((int)m, (int)tot);
-    pair_sync(pc);
-    pair_sync(pc);                 // HALF 1 has published the final state
-    m = (uint32_t)st1->x;
-    tot = (uint32_t)st1->y;
-  } else {
-    *st1 = make_int2((int)m, (int)tot);
-    pair_sync(pc);
-  }
+  m = (uint32_t)pc.xch[(NPART - 1) * kS + row].x;
+  tot = (uint32_t)pc.xch[(NPART - 1) * kS + row].y;
   const uint32_t inv = (255u * 256u) / (tot < 1 ? 1 : tot);
   tmem_walk<2>(addr,
                [&](auto gg, const uint32_t(&v)[32]) {

@@ -166,14 +166,15 @@ class ITAEngine:
     def forward_stages(self, x: torch.Tensor, fused_debug: bool = False,
                        stream: Optional[torch.cuda.Stream] = None) -> Dict[str, torch.Tensor]:
         """All golden-model intermediates.  ``fused_debug=True`` runs the fused tcgen05 kernel with its on-chip
-        intermediates dumped instead of the staged kernels (``Out`` is then a copy of ``Y``)."""
+        intermediates dumped instead of the staged kernels (one head: ``Out`` is then a copy of ``Y``; the multi-head
+        kernels dump ``Out`` themselves)."""
         B = self._batch_of(x)
         t = self._alloc_stages(B)
         st = L.MhaStages(*(C.c_void_p(t[k].data_ptr()) for k in ("Qp", "Kp", "Vp", "A", "Asm", "O", "Out")))
         fn = self.lib.ita_mha_forward_fused_debug if fused_debug else self.lib.ita_mha_forward_stages
         L.check(fn(self._h, C.c_void_p(x.data_ptr()), C.c_void_p(t["Y"].data_ptr()), B, C.byref(st),
                    _stream_ptr(stream, self.device)), fn.__name__)
-        if fused_debug:
+        if fused_debug and self.H == 1:
             t["Out"] = t["Y"].reshape(B, 1, self.S, self.E).clone()
         return t
 

@@ -210,18 +210,21 @@ class ITAViTLSTM(nn.Module):
             self._engines[key] = engs
         return self._engines[key]
 
+    @torch.no_grad()
     def tokens(self, img: torch.Tensor) -> torch.Tensor:
         """OverlapPatchMerging (``models/ITA/QAT/layers.py:25-45``): [B,1,60,90] -> [B,128,E] f32."""
         x = self.tokenizer_conv(img)
         x = F.interpolate(x, size=(8, 16), mode="bilinear", align_corners=False)
         return self.tokenizer_norm(x.flatten(2).transpose(1, 2)).contiguous()
 
+    @torch.no_grad()
     def encode(self, x: torch.Tensor) -> torch.Tensor:
         """The encoder stack on f32 tokens [B,128,E] (``QAT/model.py:100-113``): libita_b200 only."""
         for eng, lp in self._layer_engines(x.device):
             x = eng.layer(x, lp)
         return x
 
+    @torch.no_grad()
     def head(self, x: torch.Tensor, vel: torch.Tensor, quat: torch.Tensor, hidden=None):
         """Fusion, decoder, LSTM step, output layer (``QAT/model.py:116-132``)."""
         B = x.shape[0]

@@ -552,14 +552,64 @@ def test_full_size_properties(ita, R, RC):
 
 
 def test_multi_head_full_config3_sample(ita, R, RC):
-    """BASELINE configs[2] dims (H=4, S=256, E=128, P=64) on a 64-frame sample, both ITAmax variants."""
+    """BASELINE configs[2] dims (H=4, S=256, E=128, P=64) on a 64-frame sample, both ITAmax variants, on the tcgen05
+    multi-head kernels (k_ita_mh + k_ita_mh_out)."""
     for sm in (0, 1):
         p = R.make_synthetic(256, 128, 64, 4, seed=2, softmax_mode=sm)
         X = R.make_input(64, 256, 128, seed=5)
         eng = _engine(ita, p)
-        y = eng.forward(torch.from_numpy(X).to(_dev()))
+        assert eng.fused_supported, eng.fused_unsupported_reason()
+        assert "k_ita_mh" in eng.describe()
+        y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
         eng.sync_check()
         _cmp(y, RC.mha(p, X, intermediates=False)["Y"], f"config 3 sample softmax={sm}")
+        eng.close()
+
+
+@pytest.mark.parametrize("round_mode", [0, 1, 2])
+@pytest.mark.parametrize("softmax_mode", [0, 1])
+@pytest.mark.parametrize("head_mode", [0, 1])
+@pytest.mark.parametrize("H", [4, 1, 3])
+def test_multi_head_every_intermediate_vs_oracle(ita, R, round_mode, softmax_mode, head_mode, H):
+    """Config 3 dims (S=256, E=128, P=64) on the multi-head tcgen05 kernels with every on-chip intermediate dumped (Qp, Kp,
+    Vp, A, Asm, O per head, Out, Y): bit-exact vs the oracle for 3 roundings x 2 ITAmax variants x both head conventions
+    (per-head step6_O + step7_Osum / the module's concatenated projection), ragged batch (5 frames, fewer than the SMs)."""
+    if H == 1 and head_mode == 1:
+        pytest.skip("one head: the conventions coincide")
+    p = R.make_synthetic(256, 128, 64, H, seed=7 + H, rand_add=True, round_mode=round_mode, softmax_mode=softmax_mode,
+                         head_mode=head_mode)
+    eng = _engine(ita, p)
+    assert eng.fused_supported, eng.fused_unsupported_reason()
+    X = R.make_input(5, 256, 128, seed=41)
+    X[0] = 127
+    X[1] = -128
+    ref = R.mha_forward(p, X)
+    st = eng.forward_stages(torch.from_numpy(X).to(_dev()), fused_debug=True)
+    for k in STAGES + ("Out",):
+        _cmp(st[k], ref[k], f"multi-head {k} H={H} round={round_mode} softmax={softmax_mode} heads={head_mode}")
+    y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
+    eng.sync_check()
+    _cmp(y, ref["Y"], "multi-head forward Y")
+    eng.close()
+
+
+@pytest.mark.parametrize("fp", ["2", "1", "0"])
+def test_multi_head_requant_forms_and_batches(ita, R, RC, fp, monkeypatch):
+    """The multi-head kernels in every requant form (ITA_FUSED_FP: 2 = two-FFMA / one-FFMA offset forms, 1 = three-FFMA, 0 =
+    conversion / 64-bit integer forms), batches around the SM count (1 frame; 149 and 300: several frames per CTA, ragged),
+    against the C oracle and the staged kernels."""
+    monkeypatch.setenv("ITA_FUSED_FP", fp)
+    for rm in (0, 2):
+        p = R.make_synthetic(256, 128, 64, 4, seed=3, rand_add=(rm != 2), round_mode=rm, head_mode=1)
+        eng = _engine(ita, p)
+        assert eng.fused_supported, eng.fused_unsupported_reason()
+        for B in (1, 149, 300):
+            X = R.make_input(B, 256, 128, seed=50 + B)
+            x = torch.from_numpy(X).to(_dev())
+            y = eng.forward(x, path=ita.PATH_FUSED)
+            eng.sync_check()
+            _cmp(y, RC.mha(p, X, intermediates=False)["Y"], f"multi-head B={B} round={rm} ITA_FUSED_FP={fp} [{eng.describe()}]")
+        assert torch.equal(eng.forward(x, path=ita.PATH_FUSED), eng.forward(x, path=ita.PATH_STAGED))
         eng.close()
 
 
