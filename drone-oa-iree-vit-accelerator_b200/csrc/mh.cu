@@ -57,7 +57,7 @@ int mh_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   if (!(P == 64 && E == 128)) return no("multi-head tcgen05 kernel is instantiated for E = 128, P = 64");
   if (H < 1 || H > MhCfg<128, 64>::kMaxH) return no("multi-head tcgen05 kernel needs 1 <= H <= 8");
   const bool per_head = (h->head_mode == ITA_HEADS_PYITA) && H > 1;
-  if (per_head && H * E > 512) return no("per-head output projection needs H * E <= 512 tensor-memory columns");
+  if (per_head && H * E / 2 > 256) return no("per-head output projection needs H * E / 2 <= 256 tensor-memory columns per unit");
   int cc_major = 0, max_smem = 0;
   ITA_CUDA_TRY(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, h->device));
   ITA_CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
@@ -308,9 +308,28 @@ int mh_forward(ita_mha_handle *h, const int8_t *x, int8_t *y, int64_t B, const i
     pa.dQ = dump->Qp; pa.dK = dump->Kp; pa.dV = dump->Vp; pa.dA = dump->A; pa.dAsm = dump->Asm;
   }
   long long ctas = std::min<long long>(B, h->sm_count);
+#ifdef ITA_TRACE
+  static long long *trace_dev = nullptr;
+  const size_t trace_n = (size_t)(640 / 32) * (kTraceIters + 1) * 32 * 4;
+  const char *trace_file = getenv("ITA_TRACE_FILE");
+  if (!trace_dev) cudaMalloc(&trace_dev, trace_n * sizeof(long long));
+  if (trace_file) cudaMemsetAsync(trace_dev, 0, trace_n * sizeof(long long), s);
+  pa.trace = trace_dev;
+#endif
   (dump ? pl->fa_dump : pl->fa)<<<(unsigned)ctas, kMhThreads, pl->smem_a, s>>>(xmap, pa);
   count_launch();
   ITA_CUDA_TRY(cudaGetLastError());
+#ifdef ITA_TRACE
+  if (trace_file) {
+    std::vector<long long> t(trace_n);
+    cudaStreamSynchronize(s);
+    cudaMemcpy(t.data(), trace_dev, trace_n * sizeof(long long), cudaMemcpyDeviceToHost);
+    if (FILE *fp = fopen(trace_file, "wb")) {
+      fwrite(t.data(), sizeof(long long), trace_n, fp);
+      fclose(fp);
+    }
+  }
+#endif
   MoParams pb{};
   pb.wo = pl->wo; pb.rq = pl->rq_o_dev; pb.rq_sum = pl->rq_sum; pb.y = y; pb.dOut = dump ? dump->Out : nullptr; pb.batch = B; pb.H = H;
   pb.abort_flag = h->abort_flag;

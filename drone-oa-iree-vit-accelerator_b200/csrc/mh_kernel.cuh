@@ -60,6 +60,7 @@ struct MhParams {
   int torch_fast;
   int8_t *dQ, *dK, *dV, *dA;   // debug dumps (natural layouts), any may be null
   uint8_t *dAsm;
+  long long *trace;          // developer builds (-DITA_TRACE): [warp][iteration < 8][position][4] SM clock stamps of CTA 0
 };
 
 template <int E, int P>
@@ -81,7 +82,8 @@ struct MhCfg {
   static constexpr int OFF_V = OFF_K + 2 * kMhS * P;              // 2 buffers
   static constexpr int OFF_ASM = OFF_V + 2 * kMhS * P;            // [128 x 256] u8
   static constexpr int OFF_XCHG = OFF_ASM + kS * kMhS;            // [parts][128] int2
-  static constexpr int OFF_BAR = OFF_XCHG + kMhParts * kS * 8;
+  static constexpr int OFF_RQ = OFF_XCHG + kMhParts * kS * 8;     // [kMaxH][6] stage constants (a copy of MhParams::rq)
+  static constexpr int OFF_BAR = OFF_RQ + kMaxH * 6 * (int)sizeof(FRq);
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static_assert(WB_BYTES % 128 == 0 && OFF_X % 128 == 0, "alignment");
   static_assert(MB_COUNT * 8 + 8 <= 256, "barrier area");
@@ -130,6 +132,12 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
     fence_mbar_init();
   }
   if (warp == kMhEpiWarps + 1) tmem_alloc<512>(s_tmem);
+  {   // the per-head stage constants are read at the start of every position: keep them in shared memory
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(prm.rq);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(smem + C::OFF_RQ);
+    for (int i = threadIdx.x; i < H * 6 * (int)(sizeof(FRq) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  const FRq *const rq_tab = reinterpret_cast<const FRq *>(smem + C::OFF_RQ);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -183,8 +191,10 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
           constexpr int r = C::region_of(pos), t = C::tile_of(pos);
           if (!ok) return;
           if ((pos & 1) ? !nxt : !own) return;
+          ITA_TR(prm, warp, it, pos, 0);
           if (use[r] > 0) ok = mbar_wait(bars + MB_EMPTY + r, (use[r] - 1) & 1, prm.abort_flag);
           if (!ok) return;
+          ITA_TR(prm, warp, it, pos, 1);
           tc_fence_after();
           const uint32_t d = tmem_base + C::region_col(r);
           if constexpr (pos == 0 || pos == 4) {
@@ -248,6 +258,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
               umma_i8(d, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, col0 * 16 + (E / 16) * C::PW * 16, C::PW * 16, 128), IDD, 1);
             }
           }
+          ITA_TR(prm, warp, it, pos, 2);
           if (leader) {
             umma_commit(bars + MB_FULL + r);
             if constexpr (pos == 7) {
@@ -257,6 +268,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
           }
           __syncwarp();
           ++use[r];
+          ITA_TR(prm, warp, it, pos, 3);
         });
       }
     }
@@ -285,21 +297,24 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
         constexpr int r = C::region_of(pos), t = C::tile_of(pos);
         if (!ok) return;
         if ((pos & 1) ? !nxt : !own) return;
+        ITA_TR(prm, warp, it, pos, 0);
         ok = mbar_wait(bars + MB_FULL + r, use[r] & 1, prm.abort_flag);
         ++use[r];
         if (!ok) return;
+        ITA_TR(prm, warp, it, pos, 1);
         tc_fence_after();
         auto release = make_release(
             [&] {
               tc_fence_before();
               __syncwarp();
               if (lane == 0) mbar_arrive(bars + MB_EMPTY + r);
+              ITA_TR(prm, warp, it, pos, 2);
             },
             [] {});
         const int row = t * kS + rowin;                      // row inside the frame
         if constexpr (pos == 0 || pos == 4) {
           // ---- logits tile: this part's 64 key columns -> ITAmax -> Asm (u8)
-          const FRq rq = prm.rq[ho * 6 + STG_S];
+          const FRq rq = rq_tab[ho * 6 + STG_S];
           const uint32_t taddr = t_lane + C::region_col(RG_S) + (uint32_t)part * 64u;
           int8_t *gA = nullptr;
           uint8_t *gAsm = nullptr;
@@ -319,7 +334,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
           if (lane == 0) mbar_arrive(bars + MB_POS + pos);
         } else if constexpr (pos == 2 || pos == 6) {
           // ---- context chunk: 16 columns per part -> requant -> global O [B, H, 256, P]
-          const FRq rq = prm.rq[ho * 6 + STG_AV];
+          const FRq rq = rq_tab[ho * 6 + STG_AV];
           uint32_t v[16];
           tmem_ld16(t_lane + C::region_col(r) + (uint32_t)part * 16u, v);
           tmem_ld_wait();
@@ -329,7 +344,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
         } else if constexpr (pos == 1 || pos == 5) {
           // ---- Q | K projection chunk: parts 0, 1 -> Q columns [0, 32), [32, 64); parts 2, 3 -> K columns
           const int stage = part < 2 ? STG_Q : STG_K, col = (part & 1) * 32;
-          const FRq rq = prm.rq[hn * 6 + stage];
+          const FRq rq = rq_tab[hn * 6 + stage];
           uint32_t v[32];
           tmem_ld32(t_lane + C::region_col(r) + (uint32_t)part * 32u, v);
           tmem_wait32(v);
@@ -345,7 +360,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
           if (lane == 0) mbar_arrive(bars + MB_POS + pos);
         } else {
           // ---- V projection chunk: 16 columns per part
-          const FRq rq = prm.rq[hn * 6 + STG_V];
+          const FRq rq = rq_tab[hn * 6 + STG_V];
           uint32_t v[16];
           tmem_ld16(t_lane + C::region_col(r) + (uint32_t)part * 16u, v);
           tmem_ld_wait();
@@ -359,6 +374,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
           __syncwarp();
           if (lane == 0) mbar_arrive(bars + MB_POS + pos);
         }
+        ITA_TR(prm, warp, it, pos, 3);
       });
     }
   }
@@ -375,9 +391,14 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
 // ---------------------------------------------------------------------------------------------------- output projection
 // k_ita_mh_out: item = (frame, row tile).  A operand: the context rows of every head, [128 x P] per head (TMA from
 // O [B, H, 256, P]); B: Wo^T [E rows, K = H*P] plus digit blocks [E x 64] (one for the concatenated form, one per head for
-// the per-head form).  Concatenated form: one accumulator [128 x E], double-buffered in TMEM.  Per-head form (HEADS_PYITA):
-// one accumulator per head (H * E <= 512 columns), requantised per head (step6_O), summed, requantised again (step7_Osum).
-// Roles: warps 0-7 epilogue (quad = w & 3, half = w >> 2: E/2 columns each), warp 8 MMA issue, warp 9 loader + TMEM alloc.
+// the per-head form).
+//   concatenated form   one accumulator [128 x E] over every head, double-buffered in TMEM, requantised once
+//   per-head form       (HEADS_PYITA: step6_O per head, then step7_Osum) an item is two "units" of E/2 output columns; a unit
+//                       has one [128 x E/2] accumulator per head (H * E/2 <= 256 columns), two units alternate in TMEM.  The
+//                       epilogue requantises each head (biased bytes y + 128, saturated by the pack), adds the heads in 16-bit
+//                       lanes (two elements per register) and maps the sum through a shared-memory table of the step7_Osum
+//                       requantisation (the sum has at most 255 * H + 1 values, so the table is exact for every rounding mode).
+// Roles: warps 0-7 epilogue (quad = w & 3, half = w >> 2), warp 8 MMA issue, warp 9 loader + TMEM alloc.
 constexpr int kMoThreads = 10 * 32;
 constexpr int kMoStages = 3;              // context tiles in flight
 enum { MO_W = 0, MO_IN = 1 /* +stage */, MO_INFREE = 4 /* +stage */, MO_FULL = 7 /* +acc */, MO_EMPTY = 9 /* +acc */, MO_COUNT = 11 };
@@ -396,13 +417,15 @@ struct MoParams {
 template <int E, int P>
 struct MoCfg {
   static constexpr int kMaxH = 4;
+  static constexpr int kLutBytes = 1024;                         // step7_Osum table: index = sum of the biased head outputs
   static constexpr int wo_bytes(int H) { return E * H * P; }
   static constexpr int dig_bytes = E * kBiasKO;
   static constexpr int w_bytes(int H, bool per_head) { return wo_bytes(H) + (per_head ? H : 1) * dig_bytes + kConstABytes; }
   static constexpr int in_bytes(int H) { return kS * H * P; }
   static constexpr int OFF_W = 0;
   static constexpr int off_in(int H, bool per_head) { return ((w_bytes(H, per_head) + 127) / 128) * 128; }
-  static constexpr int off_bar(int H, bool per_head) { return off_in(H, per_head) + kMoStages * in_bytes(H); }
+  static constexpr int off_lut(int H, bool per_head) { return off_in(H, per_head) + kMoStages * in_bytes(H); }
+  static constexpr int off_bar(int H, bool per_head) { return off_lut(H, per_head) + kLutBytes; }
   static constexpr int smem_bytes(int H, bool per_head) { return off_bar(H, per_head) + 128; }
 };
 
@@ -414,10 +437,13 @@ __global__ void __launch_bounds__(kMoThreads, 1) k_ita_mh_out(const __grid_const
   const int off_in = C::off_in(H, PER_HEAD), in_bytes = C::in_bytes(H);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + C::off_bar(H, PER_HEAD));
   uint32_t *s_tmem = reinterpret_cast<uint32_t *>(bars + MO_COUNT);
+  int8_t *const lut = reinterpret_cast<int8_t *>(smem + C::off_lut(H, PER_HEAD));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long total = prm.batch * kMhTiles;            // items
   const long long n_items = ((long long)blockIdx.x < total) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  constexpr int NACC = PER_HEAD ? 1 : 2;                   // accumulator sets in TMEM
+  constexpr int NU = PER_HEAD ? 2 : 1;                     // units per item (per-head form: two column halves)
+  constexpr int UW = E / NU;                               // output columns of a unit
+  constexpr uint32_t ACC_COLS = 256;                       // TMEM columns of one accumulator set
   if (threadIdx.x == 0) {
     mbar_init(bars + MO_W, 1);
     for (int s = 0; s < kMoStages; ++s) {
@@ -431,6 +457,10 @@ __global__ void __launch_bounds__(kMoThreads, 1) k_ita_mh_out(const __grid_const
     fence_mbar_init();
   }
   if (warp == 9) tmem_alloc<512>(s_tmem);
+  if constexpr (PER_HEAD) {
+    const Rq rs = prm.rq_sum;
+    for (int i = threadIdx.x; i < C::kLutBytes; i += blockDim.x) lut[i] = (int8_t)requant_general(i - 128 * H, rs);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -467,103 +497,125 @@ __global__ void __launch_bounds__(kMoThreads, 1) k_ita_mh_out(const __grid_const
       bool ok = mbar_wait(bars + MO_W, 0, prm.abort_flag);
       const uint32_t w16 = smem_u32(smem + C::OFF_W) >> 4;
       constexpr int DSG = rqm_offset(MODE) ? 0 : 1;
-      constexpr uint32_t ID = make_idesc_i8(kS, E, 1, 1, 0, 0), IDD = make_idesc_i8(kS, E, DSG, DSG, 0, 0);
+      constexpr uint32_t ID = make_idesc_i8(kS, UW, 1, 1, 0, 0), IDD = make_idesc_i8(kS, UW, DSG, DSG, 0, 0);
+      long long un = 0;                                      // running unit number: accumulator set un & 1, its (un >> 1)-th use
       for (long long i = 0; i < n_items && ok; ++i) {
-        const int s = (int)(i % kMoStages), a = (int)(i % NACC);
-        const long long u = i / kMoStages, ua = i / NACC;
-        if (ua > 0) ok = mbar_wait(bars + MO_EMPTY + a, (uint32_t)((ua - 1) & 1), prm.abort_flag);
-        if (ok) ok = mbar_wait(bars + MO_IN + s, (uint32_t)(u & 1), prm.abort_flag);
-        if (!ok) break;
-        tc_fence_after();
+        const int s = (int)(i % kMoStages);
+        const long long u = i / kMoStages;
+        ok = mbar_wait(bars + MO_IN + s, (uint32_t)(u & 1), prm.abort_flag);
         const uint32_t in16 = (smem_u32(smem + off_in) >> 4) + s * (in_bytes / 16);
-        if (leader) {
-          for (int h = 0; h < H; ++h) {
-            const uint32_t d = tmem_base + (PER_HEAD ? h * E : a * E);
-            const bool first = PER_HEAD || h == 0;
-            if (first) {
-              // digit steps: bias (+ offset) of this accumulator; the offset forms use both 32-column steps
-              const uint32_t dg = off_dig + (PER_HEAD ? h : 0) * C::dig_bytes;
-              umma_i8(d, make_smem_desc_rel(w16, off_ca, 128, 0), make_smem_desc_rel(w16, dg, E * 16, 128), IDD, 0);
-              if (rqm_offset(MODE))
-                umma_i8(d, make_smem_desc_rel(w16, off_ca + 256, 128, 0), make_smem_desc_rel(w16, dg + 2 * E * 16, E * 16, 128), IDD, 1);
-            }
 #pragma unroll
-            for (int k = 0; k < P / 32; ++k)
-              umma_i8(d, make_smem_desc_rel(in16, (h * (P / 16) + 2 * k) * kS * 16, kS * 16, 128),
-                      make_smem_desc_rel(w16, (h * (P / 16) + 2 * k) * E * 16, E * 16, 128), ID, 1);
+        for (int c = 0; c < NU; ++c, ++un) {
+          const int a = (int)(un & 1);
+          const long long ua = un >> 1;
+          if (ok && ua > 0) ok = mbar_wait(bars + MO_EMPTY + a, (uint32_t)((ua - 1) & 1), prm.abort_flag);
+          if (!ok) break;
+          tc_fence_after();
+          if (leader) {
+            const uint32_t n0 = (uint32_t)(c * UW * 16);        // first output column of the unit, as a row offset of the B panels
+            for (int h = 0; h < H; ++h) {
+              const uint32_t d = tmem_base + a * ACC_COLS + (PER_HEAD ? h * UW : 0);
+              if (PER_HEAD || h == 0) {
+                // digit steps: bias (+ offset) of this accumulator; the offset forms use both 32-column steps
+                const uint32_t dg = off_dig + (PER_HEAD ? h : 0) * C::dig_bytes + n0;
+                umma_i8(d, make_smem_desc_rel(w16, off_ca, 128, 0), make_smem_desc_rel(w16, dg, E * 16, 128), IDD, 0);
+                if (rqm_offset(MODE))
+                  umma_i8(d, make_smem_desc_rel(w16, off_ca + 256, 128, 0), make_smem_desc_rel(w16, dg + 2 * E * 16, E * 16, 128), IDD, 1);
+              }
+#pragma unroll
+              for (int k = 0; k < P / 32; ++k)
+                umma_i8(d, make_smem_desc_rel(in16, (h * (P / 16) + 2 * k) * kS * 16, kS * 16, 128),
+                        make_smem_desc_rel(w16, (h * (P / 16) + 2 * k) * E * 16 + n0, E * 16, 128), ID, 1);
+            }
+            umma_commit(bars + MO_FULL + a);
+            if (c == NU - 1) umma_commit(bars + MO_INFREE + s);
           }
-          umma_commit(bars + MO_FULL + a);
-          umma_commit(bars + MO_INFREE + s);
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   } else {
     const int quad = warp & 3, half = warp >> 2;
     const int rowin = quad * 32 + lane;
     const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16);
-    constexpr int HW = E / 2;                               // columns per warp
+    constexpr int HW = UW / 2;                              // columns per warp and unit
     bool ok = true;
+    long long un = 0;
     for (long long i = 0; i < n_items && ok; ++i) {
-      const int a = (int)(i % NACC);
-      const long long ua = i / NACC;
-      ok = mbar_wait(bars + MO_FULL + a, (uint32_t)(ua & 1), prm.abort_flag);
-      if (!ok) break;
-      tc_fence_after();
       const long long item = blockIdx.x + i * (long long)gridDim.x;
       const long long f = item / kMhTiles;
       const int row = (int)(item % kMhTiles) * kS + rowin;
-      int8_t *g = prm.y + (f * kMhS + row) * (long long)E + half * HW;
-      auto release = make_release(
-          [&] {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bars + MO_EMPTY + a);
-          },
-          [] {});
-      if constexpr (!PER_HEAD) {
-        const FRq rq = prm.rq[0];
-        tmem_walk<HW / 32>([&](int gi) { return t_lane + (uint32_t)(a * E + half * HW + gi * 32); },
-                           [&](auto gg, const uint32_t(&v)[32]) {
-                             constexpr int gi = decltype(gg)::value;
-                             requant_store32<MODE, 0>(v, rq, nullptr, rowin, 0, g + gi * 32);
-                           },
-                           release);
-      } else {
-        // per head: requantise (step6_O), accumulate the s8 values, requantise the sum (step7_Osum)
-        const Rq rs = prm.rq_sum;
-#pragma unroll 1
-        for (int gi = 0; gi < HW / 16; ++gi) {
-          int acc[16];
 #pragma unroll
-          for (int e = 0; e < 16; ++e) acc[e] = 0;
+      for (int c = 0; c < NU; ++c, ++un) {
+        const int a = (int)(un & 1);
+        const long long ua = un >> 1;
+        ok = mbar_wait(bars + MO_FULL + a, (uint32_t)(ua & 1), prm.abort_flag);
+        if (!ok) break;
+        tc_fence_after();
+        const int col = c * UW + half * HW;                    // first output column of this warp
+        int8_t *g = prm.y + (f * kMhS + row) * (long long)E + col;
+        auto release = make_release(
+            [&] {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(bars + MO_EMPTY + a);
+            },
+            [] {});
+        if constexpr (!PER_HEAD) {
+          const FRq rq = prm.rq[0];
+          tmem_walk<HW / 32>([&](int gi) { return t_lane + (uint32_t)(a * ACC_COLS + half * HW + gi * 32); },
+                             [&](auto gg, const uint32_t(&v)[32]) {
+                               constexpr int gi = decltype(gg)::value;
+                               requant_store32<MODE, 0>(v, rq, nullptr, rowin, 0, g + gi * 32);
+                             },
+                             release);
+        } else {
+          static_assert(!PER_HEAD || HW == 32, "per-head form: 32 columns per warp and unit");
+          uint32_t lo[8], hi[8];                               // 16-bit lane sums of the biased head outputs: elements (4q, 4q+2) / (4q+1, 4q+3)
+#pragma unroll
+          for (int q = 0; q < 8; ++q) lo[q] = hi[q] = 0;
           for (int h = 0; h < H; ++h) {
             const FRq rq = prm.rq[h];
-            uint32_t v[16];
-            tmem_ld16(t_lane + (uint32_t)(h * E + half * HW + gi * 16), v);
-            tmem_ld_wait();
-            int yv[16];
+            uint32_t v[32];
+            tmem_ld32(t_lane + (uint32_t)(a * ACC_COLS + h * UW + half * HW), v);
+            tmem_wait32(v);
+            if (h == H - 1) release.issue();
+            uint32_t w[8];
 #pragma unroll
-            for (int e = 0; e < 16; ++e) {
-              if constexpr (rqm_offset(MODE)) yv[e] = min(max(rq_off_bits<MODE>(v[e], rq), 0), 255) - 128;
-              else yv[e] = min(max(rq_apply<MODE, 0>((int)v[e], rq, 0), -128), 127);
-              acc[e] += yv[e];
+            for (int q = 0; q < 8; ++q) {
+              int y[4];
+              uint32_t ub;                                     // y + 128 per byte
+              if constexpr (rqm_offset(MODE)) {
+                rq_off_bits2<MODE>(v[q * 4], v[q * 4 + 1], rq, y[0], y[1]);
+                rq_off_bits2<MODE>(v[q * 4 + 2], v[q * 4 + 3], rq, y[2], y[3]);
+                ub = pack_u8x4(y[0], y[1], y[2], y[3]);
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) y[e] = rq_apply<MODE, 0>((int)v[q * 4 + e], rq, e);
+                ub = pack_s8x4(y[0], y[1], y[2], y[3]) ^ 0x80808080u;
+              }
+              lo[q] += ub & 0x00FF00FFu;
+              hi[q] += (ub >> 8) & 0x00FF00FFu;
+              w[q] = ub ^ 0x80808080u;
             }
             if constexpr (DUMP) {
               if (prm.dOut) {
-                int8_t *go = prm.dOut + ((f * H + h) * kMhS + row) * (long long)E + half * HW + gi * 16;
-                *reinterpret_cast<uint4 *>(go) = make_uint4(pack_s8x4(yv[0], yv[1], yv[2], yv[3]), pack_s8x4(yv[4], yv[5], yv[6], yv[7]),
-                                                           pack_s8x4(yv[8], yv[9], yv[10], yv[11]), pack_s8x4(yv[12], yv[13], yv[14], yv[15]));
+                int8_t *go = prm.dOut + ((f * H + h) * kMhS + row) * (long long)E + col;
+                *reinterpret_cast<uint4 *>(go) = make_uint4(w[0], w[1], w[2], w[3]);
+                *reinterpret_cast<uint4 *>(go + 16) = make_uint4(w[4], w[5], w[6], w[7]);
               }
             }
           }
-          int yo[16];
+          uint32_t o[8];
 #pragma unroll
-          for (int e = 0; e < 16; ++e) yo[e] = requant_general(acc[e], rs);
-          *reinterpret_cast<uint4 *>(g + gi * 16) = make_uint4(pack_s8x4(yo[0], yo[1], yo[2], yo[3]), pack_s8x4(yo[4], yo[5], yo[6], yo[7]),
-                                                              pack_s8x4(yo[8], yo[9], yo[10], yo[11]), pack_s8x4(yo[12], yo[13], yo[14], yo[15]));
+          for (int q = 0; q < 8; ++q) {
+            const uint32_t b0 = (uint8_t)lut[lo[q] & 0xFFFFu], b2 = (uint8_t)lut[lo[q] >> 16], b1 = (uint8_t)lut[hi[q] & 0xFFFFu],
+                           b3 = (uint8_t)lut[hi[q] >> 16];
+            o[q] = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+          }
+          *reinterpret_cast<uint4 *>(g) = make_uint4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<uint4 *>(g + 16) = make_uint4(o[4], o[5], o[6], o[7]);
         }
-        release.issue();
       }
     }
   }
