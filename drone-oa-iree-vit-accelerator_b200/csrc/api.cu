@@ -473,6 +473,26 @@ int ita_encoder_layer_forward(ita_mha_handle *h, const ita_layer_params *lp, con
   return layer_forward(h, lp, x_dev, y_dev, batch, (cudaStream_t)cuda_stream);
 }
 
+int ita_tokenizer_forward(const void *img_dev, int32_t img_is_u8, int64_t batch, int32_t E, const float *conv_w_dev, const float *conv_b_dev,
+                          const float *ln_w_dev, const float *ln_b_dev, float ln_eps, float *tokens_dev, int8_t *tokens_q_dev, float q_scale,
+                          void *cuda_stream) {
+  if (batch < 0 || (batch > 0 && (!img_dev || !conv_w_dev || !conv_b_dev || !ln_w_dev || !ln_b_dev || (!tokens_dev && !tokens_q_dev)))) {
+    set_error("ita_tokenizer_forward: bad arguments");
+    return ITA_ERR_INVALID;
+  }
+  return launch_tokenizer(img_dev, img_is_u8, batch, E, conv_w_dev, conv_b_dev, ln_w_dev, ln_b_dev, ln_eps, tokens_dev, tokens_q_dev, q_scale,
+                          (cudaStream_t)cuda_stream);
+}
+
+int ita_fusion_conv_forward(const float *x_dev, int64_t batch, int32_t E, const float *conv_w_dev, const float *conv_b_dev, float *out_dev,
+                            void *cuda_stream) {
+  if (batch < 0 || (batch > 0 && (!x_dev || !conv_w_dev || !conv_b_dev || !out_dev))) {
+    set_error("ita_fusion_conv_forward: bad arguments");
+    return ITA_ERR_INVALID;
+  }
+  return launch_fuse_conv(x_dev, batch, E, conv_w_dev, conv_b_dev, out_dev, (cudaStream_t)cuda_stream);
+}
+
 int ita_quantize_f32(const float *x_dev, int8_t *q_dev, int64_t n, float scale, void *cuda_stream) {
   if (n < 0 || (n > 0 && (!x_dev || !q_dev)) || !(scale > 0.f)) {
     set_error("ita_quantize_f32: bad arguments");

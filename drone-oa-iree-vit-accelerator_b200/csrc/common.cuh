@@ -112,6 +112,10 @@ std::string describe_ffn(const ita_mha_handle *h);     // ffn.cu
 int launch_resid_ln(const float *x, const int8_t *q, float sq, const float *gamma, const float *beta, float eps, float *y, int8_t *yq,
                     float s_next, int64_t rows, int E, cudaStream_t s);
 int layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x, float *y, int64_t B, cudaStream_t s);
+// tokenizer.cu
+int launch_tokenizer(const void *img, int is_u8, int64_t B, int E, const float *w, const float *cb, const float *gamma, const float *beta,
+                     float eps, float *tok, int8_t *tokq, float q_scale, cudaStream_t s);
+int launch_fuse_conv(const float *x, int64_t B, int E, const float *w, const float *cb, float *out, cudaStream_t s);
 // selftest.cu
 int selftest_run(int device, std::string &report);
 int microbench_run(int device, int kind, double *out, int n_out);

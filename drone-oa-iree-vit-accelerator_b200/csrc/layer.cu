@@ -139,7 +139,7 @@ int layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x,
     const float *xb = x + (size_t)b0 * SE;
     int rc = launch_quantize(xb, xq, (int64_t)n, lp->s_attn_in, s);
     if (rc) return rc;
-    rc = h->fused ? fused_forward(h, xq, yq, nb, nullptr, s) : staged_forward(h, xq, yq, nb, nullptr, s);
+    rc = (h->fused || h->mh) ? fused_forward(h, xq, yq, nb, nullptr, s) : staged_forward(h, xq, yq, nb, nullptr, s);
     if (rc) return rc;
     rc = launch_resid_ln(xb, yq, lp->s_attn_out, lp->ln1_w, lp->ln1_b, lp->ln_eps, x1, x1q, lp->s_ffn_in, nb * h->S, h->E, s);
     if (rc) return rc;

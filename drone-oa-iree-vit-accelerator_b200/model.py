@@ -211,8 +211,34 @@ class ITAViTLSTM(nn.Module):
         return self._engines[key]
 
     @torch.no_grad()
-    def tokens(self, img: torch.Tensor) -> torch.Tensor:
-        """OverlapPatchMerging (``models/ITA/QAT/layers.py:25-45``): [B,1,60,90] -> [B,128,E] f32."""
+    def tokens(self, img: torch.Tensor, want_q: bool = False):
+        """OverlapPatchMerging (``models/ITA/QAT/layers.py:25-45``): [B,1,60,90] (or [B,60,90]) -> [B,128,E] f32, as ONE
+        libita_b200 kernel (conv 7x7 s2 + bilinear to 8x16 + LayerNorm).  ``img`` float32, or uint8 as it comes off the wire
+        (scaled by 1/255 in the kernel, ``main.cpp:168``).  ``want_q=True`` also returns the int8 tokens of the first encoder
+        layer's quant stub."""
+        if not img.is_cuda:
+            raise ValueError("ITAViTLSTM runs on CUDA tensors only (no CPU fallback)")
+        if img.dtype not in (torch.uint8, torch.float32):
+            img = img.float()
+        img = img.reshape(-1, 60, 90).contiguous()
+        B = img.shape[0]
+        tok = torch.empty((B, 128, self.E), dtype=torch.float32, device=img.device)
+        q, s_q = None, 0.0
+        if want_q:
+            q = torch.empty((B, 128, self.E), dtype=torch.int8, device=img.device)
+            s_q = float(self._layer_engines(img.device)[0][1].s_attn_in)
+        cw, cb = self.tokenizer_conv.weight.contiguous(), self.tokenizer_conv.bias.contiguous()
+        with torch.cuda.device(img.device):
+            L.check(L.load().ita_tokenizer_forward(img.data_ptr(), int(img.dtype == torch.uint8), B, self.E, cw.data_ptr(), cb.data_ptr(),
+                                                   self.tokenizer_norm.weight.data_ptr(), self.tokenizer_norm.bias.data_ptr(),
+                                                   float(self.tokenizer_norm.eps), tok.data_ptr(), q.data_ptr() if q is not None else None,
+                                                   s_q, torch.cuda.current_stream(img.device).cuda_stream), "ita_tokenizer_forward")
+        return (tok, q) if want_q else tok
+
+    @torch.no_grad()
+    def tokens_torch(self, img: torch.Tensor) -> torch.Tensor:
+        """The same stage with torch ops (cuDNN conv + ATen resize + LayerNorm): the fp32 reference the tokenizer kernel is
+        tested against, not used by ``forward``."""
         x = self.tokenizer_conv(img)
         x = F.interpolate(x, size=(8, 16), mode="bilinear", align_corners=False)
         return self.tokenizer_norm(x.flatten(2).transpose(1, 2)).contiguous()
@@ -228,12 +254,42 @@ class ITAViTLSTM(nn.Module):
     def head(self, x: torch.Tensor, vel: torch.Tensor, quat: torch.Tensor, hidden=None):
         """Fusion, decoder, LSTM step, output layer (``QAT/model.py:116-132``)."""
         B = x.shape[0]
-        x_2d = x.transpose(1, 2).reshape(B, self.E, 8, 16)
-        x_fused = torch.cat([self.pxShuffle(x_2d), self.up_sample(x_2d)], dim=1)
-        out = self.decoder(self.down_sample(x_fused).flatten(1))
+        if x.is_cuda:
+            # pixel-shuffle | bilinear upsample -> cat -> conv 3x3 as ONE libita_b200 kernel (the fused map never reaches HBM)
+            xc = x.contiguous()
+            down = torch.empty((B, 9 * 16 * 32), dtype=torch.float32, device=x.device)
+            with torch.cuda.device(x.device):
+                L.check(L.load().ita_fusion_conv_forward(xc.data_ptr(), B, self.E, self.down_sample.weight.contiguous().data_ptr(),
+                                                         self.down_sample.bias.data_ptr(), down.data_ptr(),
+                                                         torch.cuda.current_stream(x.device).cuda_stream), "ita_fusion_conv_forward")
+            out = self.decoder(down)
+        else:                                              # CPU (tests of the float stages): the stock modules
+            x_2d = x.transpose(1, 2).reshape(B, self.E, 8, 16)
+            x_fused = torch.cat([self.pxShuffle(x_2d), self.up_sample(x_2d)], dim=1)
+            out = self.decoder(self.down_sample(x_fused).flatten(1))
         out_cat = torch.cat([out, vel / 10.0, quat], dim=1).unsqueeze(0)
-        out_lstm, h = self.lstm(out_cat, hidden)
-        return self.nn_fc2(out_lstm.squeeze(0)), h
+        if not out_cat.is_cuda:
+            out_lstm, h = self.lstm(out_cat, hidden)          # CPU (tests of the float stages): the stock module
+            return self.nn_fc2(out_lstm.squeeze(0)), h
+        # One time step of the 3-layer LSTM as GEMMs over the batch (gate order i, f, g, o as nn.LSTM; dropout is inactive in
+        # eval): cuDNN's persistent RNN kernel is built for long sequences and takes ~1 ms per layer for a [1, 4096, .] step.
+        xs = out_cat.squeeze(0)
+        L_, Hd = self.lstm.num_layers, self.lstm.hidden_size
+        if hidden is None:
+            h0 = c0 = xs.new_zeros((L_, B, Hd))
+        else:
+            h0, c0 = hidden
+        hn, cn = [], []
+        for l in range(L_):
+            w_ih, w_hh = getattr(self.lstm, f"weight_ih_l{l}"), getattr(self.lstm, f"weight_hh_l{l}")
+            gates = torch.addmm(getattr(self.lstm, f"bias_ih_l{l}") + getattr(self.lstm, f"bias_hh_l{l}"), xs, w_ih.t())
+            gates.addmm_(h0[l], w_hh.t())
+            gi, gf, gg, go = gates.chunk(4, dim=1)
+            c = torch.sigmoid(gf) * c0[l] + torch.sigmoid(gi) * torch.tanh(gg)
+            xs = torch.sigmoid(go) * torch.tanh(c)
+            hn.append(xs)
+            cn.append(c)
+        return self.nn_fc2(xs), (torch.stack(hn), torch.stack(cn))
 
     @torch.no_grad()
     def forward(self, X: list):
@@ -242,4 +298,4 @@ class ITAViTLSTM(nn.Module):
         if not img.is_cuda:
             raise ValueError("ITAViTLSTM runs on CUDA tensors only (no CPU fallback)")
         hidden = X[3] if len(X) > 3 else None
-        return self.head(self.encode(self.tokens(img.float())), vel.float(), quat.float(), hidden)
+        return self.head(self.encode(self.tokens(img)), vel.float(), quat.float(), hidden)

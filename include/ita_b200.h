@@ -34,6 +34,11 @@
  *   ita_residual_layernorm, ita_encoder_layer_forward
  *       the float ops between the int8 blocks and the encoder-layer loop body
  *       models/ITA_single_layer_upsample_shuffle/QAT/model.py:100-113.
+ *   ita_tokenizer_forward
+ *       OverlapPatchMerging.forward  models/ITA/QAT/layers.py:25-45 (conv 7x7 s2 + bilinear to 8x16 + LayerNorm) fused with
+ *       the 1/255 image scaling of samples/inference_udp_FPGA_custom_dispatch/main.cpp:168 and the first quant stub.
+ *   ita_fusion_conv_forward
+ *       pixel-shuffle | upsample -> cat -> conv 3x3   models/ITA_single_layer_upsample_shuffle/QAT/model.py:116-121.
  *   ita_quantize_f32 / ita_dequantize_s8
  *       the QuantStub / DeQuantStub at the float boundary of the operator   models/ITA/QAT/layers.py:103,126.
  *
@@ -184,6 +189,22 @@ typedef struct ita_layer_params {
 } ita_layer_params;
 ITA_API int ita_encoder_layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x_dev, float *y_dev, int64_t batch,
                                       void *cuda_stream);
+
+/* The producer in front of the hot path: 60x90 depth frames -> 128 tokens of E channels (OverlapPatchMerging,
+ * models/ITA/QAT/layers.py:25-45), all DEVICE pointers.  img_dev: [batch, 60, 90] uint8 (img_is_u8 != 0; scaled by 1/255 as
+ * main.cpp:168 does) or float32.  conv_w_dev [E,1,7,7], conv_b_dev [E], ln_w_dev / ln_b_dev [E] as in the module's
+ * state_dict.  Outputs (either may be NULL): tokens_dev f32 [batch,128,E]; tokens_q_dev int8 [batch,128,E] =
+ * sat8(rne(tokens / q_scale)) (the first encoder layer's quant stub).  E in {64, 128}. */
+ITA_API int ita_tokenizer_forward(const void *img_dev, int32_t img_is_u8, int64_t batch, int32_t E, const float *conv_w_dev,
+                                  const float *conv_b_dev, const float *ln_w_dev, const float *ln_b_dev, float ln_eps, float *tokens_dev,
+                                  int8_t *tokens_q_dev, float q_scale, void *cuda_stream);
+
+/* The consumer behind the encoder: the fusion stage of ITALSTMNetVIT_QAT.forward (models/ITA_single_layer_upsample_shuffle/
+ * QAT/model.py:116-121), all DEVICE pointers: tokens x_dev f32 [batch,128,E] viewed as [E,8,16] -> PixelShuffle(2) |
+ * bilinear Upsample(16x32, align_corners=True) -> cat -> Conv2d(E/4+E -> 9, 3x3, padding 1) -> out_dev f32 [batch, 9*16*32]
+ * (the decoder's input).  conv_w_dev [9, E/4+E, 3, 3], conv_b_dev [9] as in the module's state_dict.  E in {64, 128}. */
+ITA_API int ita_fusion_conv_forward(const float *x_dev, int64_t batch, int32_t E, const float *conv_w_dev, const float *conv_b_dev,
+                                    float *out_dev, void *cuda_stream);
 
 /* float boundary: q = sat8(rne(x / scale)),  y = scale * q   (n elements, DEVICE pointers) */
 ITA_API int ita_quantize_f32(const float *x_dev, int8_t *q_dev, int64_t n, float scale, void *cuda_stream);

@@ -228,8 +228,10 @@ def test_full_model_state_dict_reader_and_float_stages(ita):
         sd[name] = torch.from_numpy(seeded.float_param(name, shape))
     m = M.ITAViTLSTM.from_state_dict(sd)
     with torch.no_grad():
-        tok = m.tokens(torch.from_numpy(q["img"]))
+        tok = m.tokens_torch(torch.from_numpy(q["img"]))     # torch twin of the CUDA tokenizer kernel (the checker on the GPU box)
         assert torch.equal(tok, torch.from_numpy(q["tokenizer_out"]))
+        with pytest.raises(ValueError):
+            m.tokens(torch.from_numpy(q["img"]))             # the product stage is the CUDA kernel: no CPU fallback
         out, (h, c) = m.head(torch.from_numpy(q["norm2_out"]), torch.from_numpy(q["vel"]), torch.from_numpy(q["quat"]))
         assert np.abs(out.numpy() - q["out"]).max() <= 1e-6 and np.abs(h.numpy() - q["hn"]).max() <= 1e-6
     with pytest.raises(ValueError):

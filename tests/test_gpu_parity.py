@@ -512,8 +512,9 @@ def test_full_model_forward_vs_reference_trace(ita, R):
         sd[name] = torch.from_numpy(seeded.float_param(name, shape))
     m = M.ITAViTLSTM.from_state_dict(sd).to(_dev())
     dev = lambda k: torch.from_numpy(q[k]).to(_dev())
-    tok = m.tokens(dev("img"))
-    assert np.abs(tok.cpu().numpy() - q["tokenizer_out"]).max() <= 1e-5
+    tok = m.tokens(dev("img"))                      # the CUDA tokenizer kernel
+    assert np.abs(tok.cpu().numpy() - q["tokenizer_out"]).max() <= 2e-5, np.abs(tok.cpu().numpy() - q["tokenizer_out"]).max()
+    assert np.abs(m.tokens_torch(dev("img")).cpu().numpy() - q["tokenizer_out"]).max() <= 2e-5
     enc = m.encode(dev("tokenizer_out")).cpu().numpy()
     d = np.abs(enc - q["norm2_out"])
     assert (d > 1e-4).mean() <= 0.01 and d.max() <= 0.25, ((d > 1e-4).mean(), d.max())
@@ -524,6 +525,88 @@ def test_full_model_forward_vs_reference_trace(ita, R):
     # second step: the recurrent state goes back in (the trace's second call flipped the batch)
     out2, (hn2, _) = m([torch.flip(dev("img"), dims=[0]), dev("vel"), dev("quat"), (hn, cn)])
     assert np.abs(out2.cpu().numpy() - q["out2"]).max() <= 5e-3 and np.abs(hn2.cpu().numpy() - q["hn2"]).max() <= 5e-3
+
+
+@pytest.mark.parametrize("E", [64, 128])
+@pytest.mark.parametrize("u8", [False, True])
+def test_tokenizer_kernel_vs_torch_fp32(ita, E, u8):
+    """``ita_tokenizer_forward`` (conv 7x7 s2 p3 + bilinear 30x45 -> 8x16 + LayerNorm, reference models/ITA/QAT/layers.py:25-45;
+    uint8 frames scaled by 1/255 as main.cpp:168) against the same stage in plain PyTorch fp32 (TF32 off).  The kernel blends
+    the four bilinear taps before the convolution (both are linear), so the sums are reordered: tolerance 2e-5 absolute on
+    O(1) LayerNorm outputs.  The fused quant stub must equal quantising the kernel's own float tokens exactly, and sit within
+    one LSB of the torch reference's on every element (a token within float noise of a rounding boundary may flip)."""
+    import ctypes as C
+    import torch.nn.functional as F
+    L = ita._lib
+    g = torch.Generator().manual_seed(5 + E)
+    B = 37
+    img8 = torch.randint(0, 256, (B, 60, 90), generator=g, dtype=torch.uint8)
+    img8[0] = 0
+    img8[1] = 255
+    imgf = torch.rand((B, 60, 90), generator=g) * 3.0 - 1.0
+    w = (torch.randn((E, 1, 7, 7), generator=g) * 0.2).to(_dev())
+    b = (torch.randn((E,), generator=g) * 0.1).to(_dev())
+    lw = (1.0 + 0.1 * torch.randn((E,), generator=g)).to(_dev())
+    lb = (0.1 * torch.randn((E,), generator=g)).to(_dev())
+    img = (img8 if u8 else imgf).to(_dev()).contiguous()
+    x = (img.float() / 255.0 if u8 else img).unsqueeze(1)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        ref = F.conv2d(x, w, b, stride=2, padding=3)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    assert tuple(ref.shape) == (B, E, 30, 45)
+    ref = F.interpolate(ref, size=(8, 16), mode="bilinear", align_corners=False)
+    ref = F.layer_norm(ref.flatten(2).transpose(1, 2), (E,), lw, lb, 1e-5).contiguous()
+    tok = torch.empty((B, 128, E), dtype=torch.float32, device=_dev())
+    q = torch.empty((B, 128, E), dtype=torch.int8, device=_dev())
+    s_q = 0.0371
+    L.check(L.load().ita_tokenizer_forward(img.data_ptr(), int(u8), B, E, w.data_ptr(), b.data_ptr(), lw.data_ptr(), lb.data_ptr(), 1e-5,
+                                           tok.data_ptr(), q.data_ptr(), s_q, torch.cuda.current_stream().cuda_stream), "ita_tokenizer_forward")
+    torch.cuda.synchronize()
+    d = (tok - ref).abs().max().item()
+    assert d <= 2e-5, d
+    inv = np.float32(1.0) / np.float32(s_q)
+    own = np.clip(np.rint(tok.cpu().numpy() * inv), -128, 127).astype(np.int8)
+    assert np.array_equal(q.cpu().numpy(), own)
+    refq = np.clip(np.rint(ref.cpu().numpy() * inv), -128, 127).astype(np.int32)
+    dq = np.abs(q.cpu().numpy().astype(np.int32) - refq)
+    assert dq.max() <= 1 and (dq != 0).mean() <= 1e-3, (dq.max(), (dq != 0).mean())
+    # float-only / int8-only outputs
+    tok2 = torch.empty_like(tok)
+    L.check(L.load().ita_tokenizer_forward(img.data_ptr(), int(u8), B, E, w.data_ptr(), b.data_ptr(), lw.data_ptr(), lb.data_ptr(), 1e-5,
+                                           tok2.data_ptr(), None, 0.0, torch.cuda.current_stream().cuda_stream), "ita_tokenizer_forward")
+    assert torch.equal(tok, tok2)
+
+
+@pytest.mark.parametrize("E", [64, 128])
+def test_fusion_conv_kernel_vs_torch_fp32(ita, E):
+    """``ita_fusion_conv_forward`` (PixelShuffle(2) | bilinear Upsample(16x32, align_corners=True) -> cat -> Conv2d 3x3 padding 1,
+    reference models/ITA_single_layer_upsample_shuffle/QAT/model.py:116-121) against the same ops in plain PyTorch fp32 (TF32
+    off).  fp32 sums in a different order: tolerance 5e-5 absolute on O(1) outputs."""
+    import torch.nn.functional as F
+    L = ita._lib
+    g = torch.Generator().manual_seed(9 + E)
+    B = 19
+    x = torch.randn((B, 128, E), generator=g).to(_dev())
+    cin = E // 4 + E
+    w = (torch.randn((9, cin, 3, 3), generator=g) * 0.05).to(_dev())
+    b = (torch.randn((9,), generator=g) * 0.1).to(_dev())
+    x2d = x.transpose(1, 2).reshape(B, E, 8, 16)
+    fused = torch.cat([F.pixel_shuffle(x2d, 2), F.interpolate(x2d, size=(16, 32), mode="bilinear", align_corners=True)], dim=1)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        ref = F.conv2d(fused, w, b, padding=1).flatten(1)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    out = torch.empty((B, 9 * 16 * 32), dtype=torch.float32, device=_dev())
+    L.check(L.load().ita_fusion_conv_forward(x.data_ptr(), B, E, w.data_ptr(), b.data_ptr(), out.data_ptr(),
+                                             torch.cuda.current_stream().cuda_stream), "ita_fusion_conv_forward")
+    torch.cuda.synchronize()
+    d = (out - ref).abs().max().item()
+    assert d <= 5e-5, d
 
 
 # ----------------------------------------------------------------------------------------------------- full-size properties
