@@ -25,13 +25,30 @@ __global__ void __launch_bounds__(128) k_tokenize(const void *__restrict__ img, 
   const long long f = blockIdx.x;
   const int t = threadIdx.x;
   if constexpr (U8) {
+    // u8 / 255.0f (a true division, as main.cpp:168) has 256 possible results: a table per CTA instead of 5400 divisions;
+    // the frame is read as 16-byte words (5400 = 337 * 16 + 8)
+    __shared__ float s_lut[256];
+    for (int i = t; i < 256; i += 128) s_lut[i] = __fdiv_rn((float)i, 255.0f);
+    __syncthreads();
     const uint8_t *src = reinterpret_cast<const uint8_t *>(img) + f * (kImgH * kImgW);
-    for (int i = t; i < kImgH * kImgW; i += 128) s_img[i] = __fdiv_rn((float)src[i], 255.0f);
+    if ((reinterpret_cast<uintptr_t>(src) & 7) == 0) {
+      const uint2 *s8 = reinterpret_cast<const uint2 *>(src);
+      for (int i = t; i < kImgH * kImgW / 8; i += 128) {
+        const uint2 v = s8[i];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          s_img[i * 8 + b] = s_lut[(v.x >> (8 * b)) & 0xFF];
+          s_img[i * 8 + 4 + b] = s_lut[(v.y >> (8 * b)) & 0xFF];
+        }
+      }
+    } else {
+      for (int i = t; i < kImgH * kImgW; i += 128) s_img[i] = s_lut[src[i]];
+    }
   } else {
     const float *src = reinterpret_cast<const float *>(img) + f * (kImgH * kImgW);
     for (int i = t; i < kImgH * kImgW; i += 128) s_img[i] = src[i];
   }
-  for (int i = t; i < kTaps * E; i += 128) s_w[(i % kTaps) * E + i / kTaps] = w[i];      // w is [E][49]
+  for (int i = t; i < kTaps * E; i += 128) s_w[i] = w[(i % E) * kTaps + i / E];          // w is [E][49]; s_w [tap][channel]
   __syncthreads();
 
   // ---- bilinear source coordinates (ATen area_pixel_compute_source_index, align_corners=False)
@@ -145,7 +162,7 @@ int launch_tokenizer(const void *img, int is_u8, int64_t B, int E, const float *
 // shared memory (never in HBM: torch writes and re-reads 160 KB per frame for the cat alone), each thread owning two
 // horizontally adjacent output pixels x 9 output channels in registers.  fp32 throughout (cuDNN's default for this conv is
 // TF32); summation order differs from the reference by float rounding only.
-constexpr int kFuH = 16, kFuW = 32, kFuOut = 9, kFuChunk = 16, kFuWPad = 12;
+constexpr int kFuH = 16, kFuW = 32, kFuOut = 9, kFuChunk = 16, kFuWPad = 12, kFuTokPad = 129;
 
 template <int E>
 __global__ void __launch_bounds__(256, 2) k_fuse_conv(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ cb,
@@ -153,15 +170,14 @@ __global__ void __launch_bounds__(256, 2) k_fuse_conv(const float *__restrict__ 
   constexpr int CIN = E / 4 + E, NCHUNK = CIN / kFuChunk;
   static_assert(CIN % kFuChunk == 0 && (E / 4) % kFuChunk == 0, "channel chunks must not straddle the shuffle / upsample boundary");
   extern __shared__ __align__(16) float sm[];
-  float *s_tok = sm;                                        // [128][E]
-  float *s_map = s_tok + 128 * E;                           // [16 channels][18 rows][34 cols] with a zero halo
+  float *s_tok = sm;                                        // [E][kFuTokPad]: channel-major (the [E, 8, 16] map), padded against bank conflicts
+  float *s_map = s_tok + E * kFuTokPad;                     // [16 channels][18 rows][34 cols] with a zero halo
   float *s_w = s_map + kFuChunk * 18 * 34;                  // [CIN][9 taps][12] (9 outputs, padded)
   const long long f = blockIdx.x;
   const int t = threadIdx.x;
   {
-    const float4 *src = reinterpret_cast<const float4 *>(x + f * 128 * E);
-    float4 *dst = reinterpret_cast<float4 *>(s_tok);
-    for (int i = t; i < 128 * E / 4; i += 256) dst[i] = src[i];
+    const float *src = x + f * 128 * E;                     // [token][channel] -> [channel][token]
+    for (int i = t; i < 128 * E; i += 256) s_tok[(i % E) * kFuTokPad + i / E] = src[i];
     for (int i = t; i < CIN * 9 * kFuWPad; i += 256) {
       const int o = i % kFuWPad, tap = (i / kFuWPad) % 9, c = i / (kFuWPad * 9);
       s_w[i] = o < kFuOut ? w[(o * CIN + c) * 9 + tap] : 0.f;            // w is [9][CIN][3][3]
@@ -184,15 +200,15 @@ __global__ void __launch_bounds__(256, 2) k_fuse_conv(const float *__restrict__ 
       float v;
       if (c < E / 4) {                                      // PixelShuffle: out[c, 2h+i, 2w+j] = in[4c + 2i + j, h, w]
         const int cs = c * 4 + (py & 1) * 2 + (px & 1);
-        v = s_tok[((py >> 1) * 16 + (px >> 1)) * E + cs];
+        v = s_tok[cs * kFuTokPad + (py >> 1) * 16 + (px >> 1)];
       } else {
         const int cu = c - E / 4;
         const float sy = sc_y * (float)py, sx = sc_x * (float)px;
         const int y0 = (int)sy, x0 = (int)sx;
         const int y1 = y0 + (y0 < 7 ? 1 : 0), x1 = x0 + (x0 < 15 ? 1 : 0);
         const float ly1 = sy - (float)y0, lx1 = sx - (float)x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
-        const float v00 = s_tok[(y0 * 16 + x0) * E + cu], v01 = s_tok[(y0 * 16 + x1) * E + cu], v10 = s_tok[(y1 * 16 + x0) * E + cu],
-                    v11 = s_tok[(y1 * 16 + x1) * E + cu];
+        const float *tc = s_tok + cu * kFuTokPad;
+        const float v00 = tc[y0 * 16 + x0], v01 = tc[y0 * 16 + x1], v10 = tc[y1 * 16 + x0], v11 = tc[y1 * 16 + x1];
         v = ly0 * (lx0 * v00 + lx1 * v01) + ly1 * (lx0 * v10 + lx1 * v11);
       }
       s_map[(cl * 18 + py + 1) * 34 + px + 1] = v;
@@ -237,7 +253,7 @@ int launch_fuse_conv(const float *x, int64_t B, int E, const float *w, const flo
     return ITA_ERR_INVALID;
   }
   const int cin = E / 4 + E;
-  const size_t smem = sizeof(float) * ((size_t)128 * E + (size_t)kFuChunk * 18 * 34 + (size_t)cin * 9 * kFuWPad);
+  const size_t smem = sizeof(float) * ((size_t)E * kFuTokPad + (size_t)kFuChunk * 18 * 34 + (size_t)cin * 9 * kFuWPad);
   static bool attr_set[2] = {false, false};
   const int which = E == 64 ? 0 : 1;
   if (!attr_set[which]) {
