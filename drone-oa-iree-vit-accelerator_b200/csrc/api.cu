@@ -493,6 +493,15 @@ int ita_fusion_conv_forward(const float *x_dev, int64_t batch, int32_t E, const 
   return launch_fuse_conv(x_dev, batch, E, conv_w_dev, conv_b_dev, out_dev, (cudaStream_t)cuda_stream);
 }
 
+int ita_lstm_cell_forward(const float *gates_dev, const float *c_prev_dev, float *h_dev, float *c_dev, int64_t batch, int32_t hidden,
+                          void *cuda_stream) {
+  if (batch < 0 || (batch > 0 && (!gates_dev || !c_prev_dev || !h_dev || !c_dev))) {
+    set_error("ita_lstm_cell_forward: bad arguments");
+    return ITA_ERR_INVALID;
+  }
+  return launch_lstm_cell(gates_dev, c_prev_dev, h_dev, c_dev, batch, hidden, (cudaStream_t)cuda_stream);
+}
+
 int ita_quantize_f32(const float *x_dev, int8_t *q_dev, int64_t n, float scale, void *cuda_stream) {
   if (n < 0 || (n > 0 && (!x_dev || !q_dev)) || !(scale > 0.f)) {
     set_error("ita_quantize_f32: bad arguments");

@@ -115,6 +115,7 @@ int layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x,
 // tokenizer.cu
 int launch_tokenizer(const void *img, int is_u8, int64_t B, int E, const float *w, const float *cb, const float *gamma, const float *beta,
                      float eps, float *tok, int8_t *tokq, float q_scale, cudaStream_t s);
+int launch_lstm_cell(const float *gates, const float *c_prev, float *h, float *c, int64_t B, int Hd, cudaStream_t s);
 int launch_fuse_conv(const float *x, int64_t B, int E, const float *w, const float *cb, float *out, cudaStream_t s);
 // selftest.cu
 int selftest_run(int device, std::string &report);

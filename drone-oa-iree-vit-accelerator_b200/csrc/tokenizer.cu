@@ -159,10 +159,11 @@ int launch_tokenizer(const void *img, int is_u8, int64_t B, int E, const float *
 //   Upsample(16x32, bilinear, align_corners=True)      [E,   16, 32]
 //   cat -> Conv2d(E/4 + E -> 9, 3x3, padding 1) -> flatten -> [9 * 16 * 32] (the decoder's input)
 // as one kernel: one CTA per frame, the token tile staged in shared memory, the fused map built 16 channels at a time in
-// shared memory (never in HBM: torch writes and re-reads 160 KB per frame for the cat alone), each thread owning two
-// horizontally adjacent output pixels x 9 output channels in registers.  fp32 throughout (cuDNN's default for this conv is
+// shared memory (never in HBM: torch writes and re-reads 160 KB per frame for the cat alone), each thread owning four
+// horizontally adjacent output pixels x 9 output channels in registers for half of the channels (the first version, two pixels
+// per thread over all channels, was bound by the shared-memory weight broadcasts, not by the FMA pipe).  fp32 throughout (cuDNN's default for this conv is
 // TF32); summation order differs from the reference by float rounding only.
-constexpr int kFuH = 16, kFuW = 32, kFuOut = 9, kFuChunk = 16, kFuWPad = 12, kFuTokPad = 129;
+constexpr int kFuH = 16, kFuW = 32, kFuOut = 9, kFuChunk = 16, kFuWPad = 12, kFuTokPad = 129, kFuMapW = 36, kFuMapCh = 18 * kFuMapW;
 
 template <int E>
 __global__ void __launch_bounds__(256, 2) k_fuse_conv(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ cb,
@@ -171,8 +172,8 @@ __global__ void __launch_bounds__(256, 2) k_fuse_conv(const float *__restrict__ 
   static_assert(CIN % kFuChunk == 0 && (E / 4) % kFuChunk == 0, "channel chunks must not straddle the shuffle / upsample boundary");
   extern __shared__ __align__(16) float sm[];
   float *s_tok = sm;                                        // [E][kFuTokPad]: channel-major (the [E, 8, 16] map), padded against bank conflicts
-  float *s_map = s_tok + E * kFuTokPad;                     // [16 channels][18 rows][34 cols] with a zero halo
-  float *s_w = s_map + kFuChunk * 18 * 34;                  // [CIN][9 taps][12] (9 outputs, padded)
+  float *s_map = s_tok + E * kFuTokPad;                     // [16 channels][18 rows][36 cols]: zero halo (row 0 / 17, col 0 / 33), rows 16-byte aligned
+  float *s_w = s_map + kFuChunk * kFuMapCh;                  // [CIN][9 taps][12] (9 outputs, padded)
   const long long f = blockIdx.x;
   const int t = threadIdx.x;
   {
@@ -182,64 +183,105 @@ __global__ void __launch_bounds__(256, 2) k_fuse_conv(const float *__restrict__ 
       const int o = i % kFuWPad, tap = (i / kFuWPad) % 9, c = i / (kFuWPad * 9);
       s_w[i] = o < kFuOut ? w[(o * CIN + c) * 9 + tap] : 0.f;            // w is [9][CIN][3][3]
     }
-    for (int i = t; i < kFuChunk * 18 * 34; i += 256) s_map[i] = 0.f;    // the halo stays zero, the interior is overwritten per chunk
+    for (int i = t; i < kFuChunk * kFuMapCh; i += 256) s_map[i] = 0.f;    // the halo stays zero, the interior is overwritten per chunk
   }
-  // this thread's two output pixels
-  const int Y = t / 16, X0 = (t % 16) * 2;
-  float acc[2][kFuOut];
+  // Convolution ownership: the two halves of the CTA split the channels of every chunk (half 0: channels 0-7, half 1: 8-15);
+  // inside a half, thread tt owns the four horizontally adjacent output pixels (Y, X0 .. X0 + 3) x 9 output channels, so one
+  // weight vector (3 x LDS.128, a broadcast) feeds 36 FMAs and the 3 x 6 input window of a channel is 6 vector loads.
+  const int half = t >> 7, tt = t & 127;
+  const int Y = tt >> 3, X0 = (tt & 7) * 4;
+  float acc[4][kFuOut];
 #pragma unroll
-  for (int o = 0; o < kFuOut; ++o) acc[0][o] = acc[1][o] = cb[o];
-  // bilinear source coordinates of the upsample branch (ATen: scale = (in - 1) / (out - 1), align_corners=True)
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int o = 0; o < kFuOut; ++o) acc[q][o] = 0.f;
+  // ---- build-phase ownership: thread t fills pixels (t / 32, t % 32) and (t / 32 + 8, t % 32) of every channel of a chunk; their
+  //      pixel-shuffle sources and bilinear taps (ATen: scale = (in - 1) / (out - 1), align_corners=True) do not depend on the
+  //      channel, so indices and the four tap weights are formed once
   const float sc_y = (float)(8 - 1) / (float)(kFuH - 1), sc_x = (float)(16 - 1) / (float)(kFuW - 1);
+  int b_map[2], b_sh_tok[2], b_sh_sub[2], b_o00[2], b_o01[2], b_o10[2], b_o11[2];
+  float b_w00[2], b_w01[2], b_w10[2], b_w11[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int py = t / kFuW + 8 * k, px = t % kFuW;
+    b_map[k] = (py + 1) * kFuMapW + px + 1;
+    b_sh_tok[k] = (py >> 1) * 16 + (px >> 1);
+    b_sh_sub[k] = (py & 1) * 2 + (px & 1);
+    const float sy = sc_y * (float)py, sx = sc_x * (float)px;
+    const int y0 = (int)sy, x0 = (int)sx;
+    const int y1 = y0 + (y0 < 7 ? 1 : 0), x1 = x0 + (x0 < 15 ? 1 : 0);
+    const float ly1 = sy - (float)y0, lx1 = sx - (float)x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
+    b_o00[k] = y0 * 16 + x0; b_o01[k] = y0 * 16 + x1; b_o10[k] = y1 * 16 + x0; b_o11[k] = y1 * 16 + x1;
+    b_w00[k] = ly0 * lx0; b_w01[k] = ly0 * lx1; b_w10[k] = ly1 * lx0; b_w11[k] = ly1 * lx1;
+  }
   for (int ch = 0; ch < NCHUNK; ++ch) {
     __syncthreads();                                        // staging done / the previous chunk's readers are done
-    // ---- build 16 channels of the fused map: 16 * 512 elements, 32 per thread (consecutive threads -> consecutive X)
-    for (int i = t; i < kFuChunk * kFuH * kFuW; i += 256) {
-      const int px = i % kFuW, py = (i / kFuW) % kFuH, cl = i / (kFuW * kFuH);
+    // ---- build 16 channels of the fused map (consecutive threads -> consecutive X: conflict-free stores)
+#pragma unroll 4
+    for (int cl = 0; cl < kFuChunk; ++cl) {
       const int c = ch * kFuChunk + cl;
-      float v;
-      if (c < E / 4) {                                      // PixelShuffle: out[c, 2h+i, 2w+j] = in[4c + 2i + j, h, w]
-        const int cs = c * 4 + (py & 1) * 2 + (px & 1);
-        v = s_tok[cs * kFuTokPad + (py >> 1) * 16 + (px >> 1)];
-      } else {
-        const int cu = c - E / 4;
-        const float sy = sc_y * (float)py, sx = sc_x * (float)px;
-        const int y0 = (int)sy, x0 = (int)sx;
-        const int y1 = y0 + (y0 < 7 ? 1 : 0), x1 = x0 + (x0 < 15 ? 1 : 0);
-        const float ly1 = sy - (float)y0, lx1 = sx - (float)x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
-        const float *tc = s_tok + cu * kFuTokPad;
-        const float v00 = tc[y0 * 16 + x0], v01 = tc[y0 * 16 + x1], v10 = tc[y1 * 16 + x0], v11 = tc[y1 * 16 + x1];
-        v = ly0 * (lx0 * v00 + lx1 * v01) + ly1 * (lx0 * v10 + lx1 * v11);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        float v;
+        if (c < E / 4) {                                    // PixelShuffle: out[c, 2h+i, 2w+j] = in[4c + 2i + j, h, w]
+          v = s_tok[(c * 4 + b_sh_sub[k]) * kFuTokPad + b_sh_tok[k]];
+        } else {
+          const float *tc = s_tok + (c - E / 4) * kFuTokPad;
+          v = b_w00[k] * tc[b_o00[k]] + b_w01[k] * tc[b_o01[k]] + b_w10[k] * tc[b_o10[k]] + b_w11[k] * tc[b_o11[k]];
+        }
+        s_map[cl * kFuMapCh + b_map[k]] = v;
       }
-      s_map[(cl * 18 + py + 1) * 34 + px + 1] = v;
     }
     __syncthreads();
-    // ---- 3x3 convolution over the chunk's channels
+    // ---- 3x3 convolution over this half's 8 channels of the chunk
 #pragma unroll 2
-    for (int cl = 0; cl < kFuChunk; ++cl) {
-      const float *mp = s_map + (cl * 18 + Y) * 34 + X0;    // top-left of the 3 x 4 input window (halo offset included)
-      float in[3][4];
+    for (int ci = 0; ci < kFuChunk / 2; ++ci) {
+      const int cl = half * (kFuChunk / 2) + ci;
+      const float *mp = s_map + cl * kFuMapCh + Y * kFuMapW + X0;     // top-left of the 3 x 6 input window (halo offset included)
+      float in[3][6];
 #pragma unroll
-      for (int r = 0; r < 3; ++r)
-#pragma unroll
-        for (int q = 0; q < 4; ++q) in[r][q] = mp[r * 34 + q];
+      for (int r = 0; r < 3; ++r) {
+        const float4 a = *reinterpret_cast<const float4 *>(mp + r * kFuMapW);
+        const float2 b2 = *reinterpret_cast<const float2 *>(mp + r * kFuMapW + 4);
+        in[r][0] = a.x; in[r][1] = a.y; in[r][2] = a.z; in[r][3] = a.w; in[r][4] = b2.x; in[r][5] = b2.y;
+      }
       const float4 *wp = reinterpret_cast<const float4 *>(s_w + (ch * kFuChunk + cl) * 9 * kFuWPad);
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
         const float4 w0 = wp[tap * 3], w1 = wp[tap * 3 + 1], w2 = wp[tap * 3 + 2];
         const float wv[kFuWPad] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w};
-        const float a0 = in[tap / 3][tap % 3], a1 = in[tap / 3][tap % 3 + 1];
 #pragma unroll
-        for (int o = 0; o < kFuOut; ++o) {
-          acc[0][o] = fmaf(wv[o], a0, acc[0][o]);
-          acc[1][o] = fmaf(wv[o], a1, acc[1][o]);
+        for (int q = 0; q < 4; ++q) {
+          const float a = in[tap / 3][tap % 3 + q];
+#pragma unroll
+          for (int o = 0; o < kFuOut; ++o) acc[q][o] = fmaf(wv[o], a, acc[q][o]);
         }
       }
     }
   }
-  float *op = out + f * (kFuOut * kFuH * kFuW) + Y * kFuW + X0;
+  // ---- add the two channel halves (through the map buffer, dead now) and the bias, store
+  __syncthreads();
+  float *red = s_map;                                       // [128 threads][36]
+  if (half == 1) {
 #pragma unroll
-  for (int o = 0; o < kFuOut; ++o) *reinterpret_cast<float2 *>(op + o * kFuH * kFuW) = make_float2(acc[0][o], acc[1][o]);
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int o = 0; o < kFuOut; ++o) red[(q * kFuOut + o) * 128 + tt] = acc[q][o];
+  }
+  __syncthreads();
+  if (half == 0) {
+    float *op = out + f * (kFuOut * kFuH * kFuW) + Y * kFuW + X0;
+#pragma unroll
+    for (int o = 0; o < kFuOut; ++o) {
+      const float bo = cb[o];
+      float4 v;
+      v.x = acc[0][o] + red[(0 * kFuOut + o) * 128 + tt] + bo;
+      v.y = acc[1][o] + red[(1 * kFuOut + o) * 128 + tt] + bo;
+      v.z = acc[2][o] + red[(2 * kFuOut + o) * 128 + tt] + bo;
+      v.w = acc[3][o] + red[(3 * kFuOut + o) * 128 + tt] + bo;
+      *reinterpret_cast<float4 *>(op + o * kFuH * kFuW) = v;
+    }
+  }
 }
 
 int launch_fuse_conv(const float *x, int64_t B, int E, const float *w, const float *cb, float *out, cudaStream_t s) {
@@ -253,7 +295,7 @@ int launch_fuse_conv(const float *x, int64_t B, int E, const float *w, const flo
     return ITA_ERR_INVALID;
   }
   const int cin = E / 4 + E;
-  const size_t smem = sizeof(float) * ((size_t)E * kFuTokPad + (size_t)kFuChunk * 18 * 34 + (size_t)cin * 9 * kFuWPad);
+  const size_t smem = sizeof(float) * ((size_t)E * kFuTokPad + (size_t)kFuChunk * kFuMapCh + (size_t)cin * 9 * kFuWPad);
   static bool attr_set[2] = {false, false};
   const int which = E == 64 ? 0 : 1;
   if (!attr_set[which]) {
@@ -268,6 +310,37 @@ int launch_fuse_conv(const float *x, int64_t B, int E, const float *w, const flo
   }
   if (E == 64) k_fuse_conv<64><<<(unsigned)B, 256, smem, s>>>(x, w, cb, out);
   else k_fuse_conv<128><<<(unsigned)B, 256, smem, s>>>(x, w, cb, out);
+  count_launch();
+  ITA_CUDA_TRY(cudaGetLastError());
+  return ITA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- LSTM cell
+// The pointwise half of one LSTM time step (nn.LSTM gate order i, f, g, o; reference model.py:68,128): the gate pre-activations
+// [B, 4*Hd] come from two cuBLAS GEMMs, this kernel turns them and c_prev into (h, c) in one pass instead of ~8 elementwise
+// launches per layer.
+__global__ void __launch_bounds__(256) k_lstm_cell(const float *__restrict__ gates, const float *__restrict__ c_prev, float *__restrict__ h,
+                                                   float *__restrict__ c, long long n, int Hd) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long b = i / Hd;
+  const int j = (int)(i - b * Hd);
+  const float *g = gates + b * 4 * Hd;
+  const float gi = 1.0f / (1.0f + expf(-g[j])), gf = 1.0f / (1.0f + expf(-g[Hd + j])), gg = tanhf(g[2 * Hd + j]),
+              go = 1.0f / (1.0f + expf(-g[3 * Hd + j]));
+  const float cn = gf * c_prev[i] + gi * gg;
+  c[i] = cn;
+  h[i] = go * tanhf(cn);
+}
+
+int launch_lstm_cell(const float *gates, const float *c_prev, float *h, float *c, int64_t B, int Hd, cudaStream_t s) {
+  if (B <= 0) return ITA_OK;
+  if (Hd <= 0) {
+    set_error("LSTM cell: bad hidden size %d", Hd);
+    return ITA_ERR_INVALID;
+  }
+  const long long n = (long long)B * Hd;
+  k_lstm_cell<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(gates, c_prev, h, c, n, Hd);
   count_launch();
   ITA_CUDA_TRY(cudaGetLastError());
   return ITA_OK;

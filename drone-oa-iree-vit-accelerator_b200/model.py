@@ -156,6 +156,7 @@ class ITAViTLSTM(nn.Module):
         self.layer_params: List[Optional[ITAQuantParams]] = [None] * num_layers
         self.layer_scales: List[Dict[str, float]] = [{} for _ in range(num_layers)]
         self._engines: Dict[int, list] = {}
+        self._lstm_bias = None                       # b_ih + b_hh per LSTM layer, formed once per device
         self.eval()
 
     # ------------------------------------------------------------------------------------------------ checkpoint
@@ -192,6 +193,7 @@ class ITAViTLSTM(nn.Module):
         for i in range(self.num_layers):
             self.layer_params[i], self.layer_scales[i] = layer_quant_params(sd, i, self.H, self.S)
         self._engines.clear()
+        self._lstm_bias = None
 
     # ------------------------------------------------------------------------------------------------ forward
     def _layer_engines(self, device: torch.device):
@@ -279,17 +281,21 @@ class ITAViTLSTM(nn.Module):
             h0 = c0 = xs.new_zeros((L_, B, Hd))
         else:
             h0, c0 = hidden
-        hn, cn = [], []
+        hn = xs.new_empty((L_, B, Hd))
+        cn = xs.new_empty((L_, B, Hd))
+        c0 = c0.contiguous()
+        lib, st = L.load(), torch.cuda.current_stream(xs.device).cuda_stream
+        if self._lstm_bias is None or self._lstm_bias[0].device != xs.device:
+            self._lstm_bias = [(getattr(self.lstm, f"bias_ih_l{l}") + getattr(self.lstm, f"bias_hh_l{l}")).detach() for l in range(L_)]
         for l in range(L_):
             w_ih, w_hh = getattr(self.lstm, f"weight_ih_l{l}"), getattr(self.lstm, f"weight_hh_l{l}")
-            gates = torch.addmm(getattr(self.lstm, f"bias_ih_l{l}") + getattr(self.lstm, f"bias_hh_l{l}"), xs, w_ih.t())
+            gates = torch.addmm(self._lstm_bias[l], xs, w_ih.t())
             gates.addmm_(h0[l], w_hh.t())
-            gi, gf, gg, go = gates.chunk(4, dim=1)
-            c = torch.sigmoid(gf) * c0[l] + torch.sigmoid(gi) * torch.tanh(gg)
-            xs = torch.sigmoid(go) * torch.tanh(c)
-            hn.append(xs)
-            cn.append(c)
-        return self.nn_fc2(xs), (torch.stack(hn), torch.stack(cn))
+            with torch.cuda.device(xs.device):
+                L.check(lib.ita_lstm_cell_forward(gates.data_ptr(), c0[l].data_ptr(), hn[l].data_ptr(), cn[l].data_ptr(), B, Hd, st),
+                        "ita_lstm_cell_forward")
+            xs = hn[l]
+        return self.nn_fc2(xs), (hn, cn)
 
     @torch.no_grad()
     def forward(self, X: list):

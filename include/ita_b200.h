@@ -206,6 +206,12 @@ ITA_API int ita_tokenizer_forward(const void *img_dev, int32_t img_is_u8, int64_
 ITA_API int ita_fusion_conv_forward(const float *x_dev, int64_t batch, int32_t E, const float *conv_w_dev, const float *conv_b_dev,
                                     float *out_dev, void *cuda_stream);
 
+/* Pointwise half of one LSTM time step (nn.LSTM gate order i, f, g, o; the model's 3-layer LSTM, QAT/model.py:68,128), DEVICE
+ * pointers: gates_dev f32 [batch, 4*hidden] (= x W_ih^T + b_ih + h W_hh^T + b_hh), c_prev_dev [batch, hidden] ->
+ * c = sigmoid(f) * c_prev + sigmoid(i) * tanh(g), h = sigmoid(o) * tanh(c).  h_dev / c_dev may alias nothing else. */
+ITA_API int ita_lstm_cell_forward(const float *gates_dev, const float *c_prev_dev, float *h_dev, float *c_dev, int64_t batch, int32_t hidden,
+                                  void *cuda_stream);
+
 /* float boundary: q = sat8(rne(x / scale)),  y = scale * q   (n elements, DEVICE pointers) */
 ITA_API int ita_quantize_f32(const float *x_dev, int8_t *q_dev, int64_t n, float scale, void *cuda_stream);
 ITA_API int ita_dequantize_s8(const int8_t *q_dev, float *y_dev, int64_t n, float scale, void *cuda_stream);
