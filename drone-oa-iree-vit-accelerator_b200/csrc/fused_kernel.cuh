@@ -362,6 +362,14 @@ __device__ __forceinline__ void tmem_pin32(uint32_t (&v)[32]) {
                : "memory");
 }
 
+__device__ __forceinline__ void tmem_pin16(uint32_t (&v)[16]) {
+  asm volatile(""
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                 "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+               :
+               : "memory");
+}
+
 // Walk NG groups of 32 accumulator columns of this thread's row, software-pipelined: the TMEM load of group g+1 is in
 // flight while f(g, v) works on group g.  addr(g) gives the TMEM address of group g.  After the last load has landed,
 // `done.issue()` runs once, and `done.finish()` after the last group has been processed (together they hand the TMEM

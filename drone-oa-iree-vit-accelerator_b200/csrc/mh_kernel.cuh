@@ -18,12 +18,12 @@
 //                   block [Wq | Wk | Wv]^T with the digit K columns + the head's offset tiles, double-buffered and streamed
 //                   from L2 (30 KB per head), the constant digit A tile.  All operands in the no-swizzle panel layout of
 //                   fused_kernel.cuh, with 256-row panels for X/Q/K/V.
-//   tensor memory   RS = 256 columns (logits tile), R0 = 128 (Q|K projection chunk), R1a / R1b = 64 each (V projection
-//                   chunk, context chunk)
-//   schedule        8 positions per iteration; even positions belong to the item in its attention phase ("own"), odd ones
-//                   are the projections of the NEXT item, placed where the own chain would otherwise bubble (A.V can only
-//                   start when ITAmax has written the last probability):
-//                       0: S t0   1: QK-proj' t0   2: AV t0   3: V-proj' t0   4: S t1   5: QK-proj' t1   6: AV t1   7: V-proj' t1
+//   tensor memory   RS = 256 columns (logits tile), RP = 192 (Q | K | V projection accumulators of one row tile), RA = 64
+//                   (context chunk)
+//   schedule        6 positions per iteration; S / AV belong to the item in its attention phase ("own"), P' are the
+//                   projections of the NEXT item, placed where the own chain would otherwise bubble (A.V can only start
+//                   when ITAmax has written the last probability):
+//                       0: S t0   1: P' t0   2: AV t0   3: S t1   4: P' t1   5: AV t1
 //                   One MMA-issuing warp walks the positions in order; 16 epilogue warps (4 TMEM lane quadrants x 4
 //                   column parts) drain every position in the same order, so "the epilogue of position p is complete"
 //                   (one mbarrier per position) orders every shared-memory hazard: Q is overwritten by the next head only
@@ -44,9 +44,10 @@ constexpr int kMhEpiWarps = 4 * kMhParts;
 constexpr int kMhThreads = (kMhEpiWarps + 2) * 32;
 
 // mbarriers of k_ita_mh
-enum { MB_CA = 0, MB_W = 1 /* +buf */, MB_WFREE = 3 /* +buf */, MB_X = 5, MB_XFREE = 6, MB_FULL = 7 /* +region */, MB_EMPTY = 11 /* +region */,
-       MB_POS = 15 /* +position */, MB_COUNT = 23 };
-enum { RG_S = 0, RG_0 = 1, RG_1A = 2, RG_1B = 3 };
+enum { MB_CA = 0, MB_W = 1 /* +buf */, MB_WFREE = 3 /* +buf */, MB_X = 5, MB_XFREE = 6, MB_FULL = 7 /* +region */, MB_EMPTY = 10 /* +region */,
+       MB_POS = 13 /* +position */, MB_COUNT = 19 };
+enum { RG_S = 0, RG_P = 1, RG_A = 2 };
+constexpr int kMhPos = 6;
 
 struct MhParams {
   const int8_t *wblocks;     // device: [H] weight blocks (MhCfg::WB_BYTES each)
@@ -89,9 +90,10 @@ struct MhCfg {
   static_assert(MB_COUNT * 8 + 8 <= 256, "barrier area");
   static_assert(SMEM_BYTES <= kSmemLimit, "does not fit shared memory");
   // TMEM columns of the four regions
-  static constexpr uint32_t region_col(int r) { return r == RG_S ? 0u : r == RG_0 ? 256u : r == RG_1A ? 384u : 448u; }
-  static constexpr int region_of(int pos) { return (pos == 0 || pos == 4) ? RG_S : (pos == 1 || pos == 5) ? RG_0 : (pos == 2 || pos == 6) ? RG_1A : RG_1B; }
-  static constexpr int tile_of(int pos) { return pos >> 2; }
+  static constexpr uint32_t region_col(int r) { return r == RG_S ? 0u : r == RG_P ? 256u : 448u; }
+  static constexpr int region_of(int pos) { return (pos == 0 || pos == 3) ? RG_S : (pos == 1 || pos == 4) ? RG_P : RG_A; }
+  static constexpr int tile_of(int pos) { return pos / 3; }
+  static constexpr bool is_next(int pos) { return pos == 1 || pos == 4; }
 };
 
 template <int E>
@@ -124,11 +126,11 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
     }
     mbar_init(bars + MB_X, 1);
     mbar_init(bars + MB_XFREE, 1);
-    for (int r = 0; r < 4; ++r) {
+    for (int r = 0; r < 3; ++r) {
       mbar_init(bars + MB_FULL + r, 1);
       mbar_init(bars + MB_EMPTY + r, kMhEpiWarps);
     }
-    for (int p = 0; p < 8; ++p) mbar_init(bars + MB_POS + p, kMhEpiWarps);
+    for (int p = 0; p < kMhPos; ++p) mbar_init(bars + MB_POS + p, kMhEpiWarps);
     fence_mbar_init();
   }
   if (warp == kMhEpiWarps + 1) tmem_alloc<512>(s_tmem);
@@ -177,7 +179,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
                      asm16 = smem_u32(smem + C::OFF_ASM) >> 4;
       constexpr int DSG = rqm_offset(MODE) ? 0 : 1;       // digit operands: unsigned for the offset forms
       constexpr uint32_t PS = C::PR * 16;                 // panel stride of the 256-row buffers
-      uint32_t use[4] = {0, 0, 0, 0};                     // uses of each TMEM region so far
+      uint32_t use[3] = {0, 0, 0};                        // uses of each TMEM region so far
       for (long long it = 0; it <= n_items && ok; ++it) {
         const bool own = it >= 1, nxt = it < n_items;
         const uint32_t php = (uint32_t)((it - 1) & 1);    // parity of "completion number `it`" of a position barrier
@@ -186,18 +188,18 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
         const uint32_t kown16 = (smem_u32(smem + C::OFF_K) >> 4) + ob * (kMhS * P / 16), vown16 = (smem_u32(smem + C::OFF_V) >> 4) + ob * (kMhS * P / 16);
         const uint32_t w16 = (smem_u32(smem + C::OFF_W) >> 4) + nb * (C::WB_BYTES / 16);
         const uint32_t ot16 = (smem_u32(smem + C::OFF_OT) >> 4) + (own ? (uint32_t)((it - 1) % H) : 0u) * (C::OT_BYTES / 16);   // the own head's offset tiles
-        static_for<0, 8>([&](auto pp) {
+        static_for<0, kMhPos>([&](auto pp) {
           constexpr int pos = decltype(pp)::value;
           constexpr int r = C::region_of(pos), t = C::tile_of(pos);
           if (!ok) return;
-          if ((pos & 1) ? !nxt : !own) return;
+          if (C::is_next(pos) ? !nxt : !own) return;
           ITA_TR(prm, warp, it, pos, 0);
           if (use[r] > 0) ok = mbar_wait(bars + MB_EMPTY + r, (use[r] - 1) & 1, prm.abort_flag);
           if (!ok) return;
           ITA_TR(prm, warp, it, pos, 1);
           tc_fence_after();
           const uint32_t d = tmem_base + C::region_col(r);
-          if constexpr (pos == 0 || pos == 4) {
+          if constexpr (pos == 0 || pos == 3) {
             // ---- logits of row tile t: A = Q rows [128 t, +128) (K = P), B = K (all 256 keys); offset digit steps first
             if (rqm_offset(MODE)) {
               constexpr uint32_t IDD = make_idesc_i8(kS, kMhS, 0, 0, 0, 0);
@@ -209,8 +211,8 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
               }
               __syncwarp();
             }
-            if constexpr (pos == 0) {        // Q, K of the own item: positions 1 and 5 of the iteration before
-              ok = mbar_wait(bars + MB_POS + 5, php, prm.abort_flag);
+            if constexpr (pos == 0) {        // Q, K, V of the own item: positions 1 and 4 of the iteration before
+              ok = mbar_wait(bars + MB_POS + 4, php, prm.abort_flag);
               if (!ok) return;
               tc_fence_after();
             }
@@ -221,16 +223,15 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
                 umma_i8(d, make_smem_desc_rel(q16, t * kS * 16 + k * 2 * PS, PS, 128), make_smem_desc_rel(kown16, k * 2 * PS, PS, 128), ID,
                         (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
             }
-          } else if constexpr (pos == 2 || pos == 6) {
+          } else if constexpr (pos == 2 || pos == 5) {
             // ---- context of row tile t: A = Asm [128, K = 256] u8, B = V [K = 256 keys, N = P] MN-major
             if (rqm_offset(MODE)) {
               constexpr uint32_t IDD = make_idesc_i8(kS, P, 0, 0, 0, 0);
               if (leader) umma_i8(d, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(ot16, C::OT_DAV, 128, 0), IDD, 0);
               __syncwarp();
             }
-            // Asm of this tile: the ITAmax epilogue of position pos - 2; V of the own item: positions 3 and 7 of the iteration before
+            // Asm of this tile: the ITAmax epilogue of position pos - 2 (V of the own item was waited for at position 0)
             ok = mbar_wait(bars + MB_POS + (pos - 2), php, prm.abort_flag);
-            if (ok && pos == 2) ok = mbar_wait(bars + MB_POS + 7, php, prm.abort_flag);
             if (!ok) return;
             tc_fence_after();
             constexpr uint32_t ID = make_idesc_i8(kS, P, 0, 1, 0, 1);
@@ -241,27 +242,31 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
                         (k > 0 || rqm_offset(MODE)) ? 1u : 0u);
             }
           } else {
-            // ---- projections of the next item, row tile t: Q | K (128 columns) at positions 1 / 5, V (64) at 3 / 7
-            constexpr int col0 = (pos == 1 || pos == 5) ? 0 : 2 * P, NC = (pos == 1 || pos == 5) ? 2 * P : P;
+            // ---- projections of the next item, row tile t: Q | K into columns [0, 128) of RP, V into [128, 192)
             if constexpr (pos == 1) {
               ok = mbar_wait(bars + MB_W + nb, (uint32_t)((it >> 1) & 1), prm.abort_flag);
               if (ok && nh == 0) ok = mbar_wait(bars + MB_X, (uint32_t)((it / H) & 1), prm.abort_flag);
               if (!ok) return;
               tc_fence_after();
             }
-            constexpr uint32_t ID = make_idesc_i8(kS, NC, 1, 1, 0, 0), IDD = make_idesc_i8(kS, NC, DSG, DSG, 0, 0);
             if (leader) {
+              static_for<0, 2>([&](auto cc) {
+                constexpr int c = decltype(cc)::value;
+                constexpr int col0 = c == 0 ? 0 : 2 * P, NC = c == 0 ? 2 * P : P;
+                constexpr uint32_t ID = make_idesc_i8(kS, NC, 1, 1, 0, 0), IDD = make_idesc_i8(kS, NC, DSG, DSG, 0, 0);
 #pragma unroll
-              for (int k = 0; k < E / 32; ++k)
-                umma_i8(d, make_smem_desc_rel(x16, t * kS * 16 + k * 2 * PS, PS, 128),
-                        make_smem_desc_rel(w16, col0 * 16 + k * 2 * C::PW * 16, C::PW * 16, 128), ID, k > 0);
-              umma_i8(d, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, col0 * 16 + (E / 16) * C::PW * 16, C::PW * 16, 128), IDD, 1);
+                for (int k = 0; k < E / 32; ++k)
+                  umma_i8(d + col0, make_smem_desc_rel(x16, t * kS * 16 + k * 2 * PS, PS, 128),
+                          make_smem_desc_rel(w16, col0 * 16 + k * 2 * C::PW * 16, C::PW * 16, 128), ID, k > 0);
+                umma_i8(d + col0, make_smem_desc_rel(ca16, 0, 128, 0), make_smem_desc_rel(w16, col0 * 16 + (E / 16) * C::PW * 16, C::PW * 16, 128),
+                        IDD, 1);
+              });
             }
           }
           ITA_TR(prm, warp, it, pos, 2);
           if (leader) {
             umma_commit(bars + MB_FULL + r);
-            if constexpr (pos == 7) {
+            if constexpr (pos == 4) {
               umma_commit(bars + MB_WFREE + nb);                   // the item's last projection has read its weight block
               if (nh == H - 1) umma_commit(bars + MB_XFREE);       // the frame's last projection has read X
             }
@@ -283,7 +288,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
     int8_t *const q_buf = reinterpret_cast<int8_t *>(smem + C::OFF_Q);
     int8_t *const asm_buf = reinterpret_cast<int8_t *>(smem + C::OFF_ASM);
     bool ok = true;
-    uint32_t use[4] = {0, 0, 0, 0};
+    uint32_t use[3] = {0, 0, 0};
     for (long long it = 0; it <= n_items && ok; ++it) {
       const bool own = it >= 1, nxt = it < n_items;
       const int nb = (int)(it & 1);
@@ -292,11 +297,11 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
       const int ho = own ? (int)(jo % H) : 0, hn = nxt ? (int)(jn % H) : 0;
       int8_t *const k_buf = reinterpret_cast<int8_t *>(smem + C::OFF_K) + nb * (kMhS * P);
       int8_t *const v_buf = reinterpret_cast<int8_t *>(smem + C::OFF_V) + nb * (kMhS * P);
-      static_for<0, 8>([&](auto pp) {
+      static_for<0, kMhPos>([&](auto pp) {
         constexpr int pos = decltype(pp)::value;
         constexpr int r = C::region_of(pos), t = C::tile_of(pos);
         if (!ok) return;
-        if ((pos & 1) ? !nxt : !own) return;
+        if (C::is_next(pos) ? !nxt : !own) return;
         ITA_TR(prm, warp, it, pos, 0);
         ok = mbar_wait(bars + MB_FULL + r, use[r] & 1, prm.abort_flag);
         ++use[r];
@@ -312,7 +317,7 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
             },
             [] {});
         const int row = t * kS + rowin;                      // row inside the frame
-        if constexpr (pos == 0 || pos == 4) {
+        if constexpr (pos == 0 || pos == 3) {
           // ---- logits tile: this part's 64 key columns -> ITAmax -> Asm (u8)
           const FRq rq = rq_tab[ho * 6 + STG_S];
           const uint32_t taddr = t_lane + C::region_col(RG_S) + (uint32_t)part * 64u;
@@ -332,44 +337,36 @@ __global__ void __launch_bounds__(kMhThreads, 1) k_ita_mh(const __grid_constant_
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(bars + MB_POS + pos);
-        } else if constexpr (pos == 2 || pos == 6) {
+        } else if constexpr (pos == 2 || pos == 5) {
           // ---- context chunk: 16 columns per part -> requant -> global O [B, H, 256, P]
           const FRq rq = rq_tab[ho * 6 + STG_AV];
           uint32_t v[16];
           tmem_ld16(t_lane + C::region_col(r) + (uint32_t)part * 16u, v);
           tmem_ld_wait();
+          tmem_pin16(v);
           release.issue();
           int8_t *g = prm.o + ((fo * H + ho) * kMhS + row) * (long long)P + part * 16;
           requant_store32<MODE, 0, false, 16, C::PR>(v, rq, nullptr, row, 0, g);
-        } else if constexpr (pos == 1 || pos == 5) {
-          // ---- Q | K projection chunk: parts 0, 1 -> Q columns [0, 32), [32, 64); parts 2, 3 -> K columns
+        } else {
+          // ---- projection accumulators of the next item's row tile: 32 of the Q | K columns (parts 0, 1 -> Q columns [0, 32),
+          //      [32, 64); parts 2, 3 -> K) and 16 of the V columns per part, loaded together
           const int stage = part < 2 ? STG_Q : STG_K, col = (part & 1) * 32;
           const FRq rq = rq_tab[hn * 6 + stage];
-          uint32_t v[32];
+          const FRq rqv = rq_tab[hn * 6 + STG_V];
+          uint32_t v[32], v2[16];
           tmem_ld32(t_lane + C::region_col(r) + (uint32_t)part * 32u, v);
-          tmem_wait32(v);
+          tmem_ld16(t_lane + C::region_col(r) + 2u * P + (uint32_t)part * 16u, v2);
+          tmem_wait32(v);                                      // tcgen05.wait::ld covers both loads
+          tmem_pin16(v2);                                      // ... and nothing that reads v2 may move above it
           release.issue();
-          int8_t *g = nullptr;
+          int8_t *g = nullptr, *g2 = nullptr;
           if constexpr (DUMP) {
             int8_t *base = part < 2 ? prm.dQ : prm.dK;
             if (base) g = base + ((fn * H + hn) * kMhS + row) * (long long)P + col;
+            if (prm.dV) g2 = prm.dV + ((fn * H + hn) * kMhS + row) * (long long)P + part * 16;
           }
           requant_store32<MODE, 0, false, 32, C::PR>(v, rq, part < 2 ? q_buf : k_buf, row, col, g);
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bars + MB_POS + pos);
-        } else {
-          // ---- V projection chunk: 16 columns per part
-          const FRq rq = rq_tab[hn * 6 + STG_V];
-          uint32_t v[16];
-          tmem_ld16(t_lane + C::region_col(r) + (uint32_t)part * 16u, v);
-          tmem_ld_wait();
-          release.issue();
-          int8_t *g = nullptr;
-          if constexpr (DUMP) {
-            if (prm.dV) g = prm.dV + ((fn * H + hn) * kMhS + row) * (long long)P + part * 16;
-          }
-          requant_store32<MODE, 0, false, 16, C::PR>(v, rq, v_buf, row, part * 16, g);
+          requant_store32<MODE, 0, false, 16, C::PR>(v2, rqv, v_buf, row, part * 16, g2);
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(bars + MB_POS + pos);

@@ -22,7 +22,7 @@ os.environ["ITA_TRACE_FILE"] = out
 eng.forward(x, path=ita.PATH_FUSED)
 torch.cuda.synchronize()
 t = np.fromfile(out, dtype=np.int64).reshape(-1, 9, 32, 4)
-names = ["S t0", "QK' t0", "AV t0", "V' t0", "S t1", "QK' t1", "AV t1", "V' t1"]
+names = ["S t0", "P' t0", "AV t0", "S t1", "P' t1", "AV t1"]
 mma = 16
 base = t[mma, it, 0, 0]
 print(f"iteration {it}: period (MMA pos 0 start -> next) = {t[mma, it + 1, 0, 0] - base} cycles")
