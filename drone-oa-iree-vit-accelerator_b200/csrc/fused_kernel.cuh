@@ -425,6 +425,26 @@ __device__ __forceinline__ void tmem_walk(A &&addr, F &&f, D &&done) {
 #endif
 }
 
+// The same walk when the caller has already issued the load of group 0 into `va` (so that it is in flight across a barrier).
+template <int NG, class A, class F, class D>
+__device__ __forceinline__ void tmem_walk_pre(uint32_t (&va)[32], A &&addr, F &&f, D &&done) {
+  uint32_t vb[32];
+  tmem_wait32(va);
+  static_for<0, NG>([&](auto gg) {
+    constexpr int g = decltype(gg)::value;
+    uint32_t(&cur)[32] = (g & 1) ? vb : va;
+    uint32_t(&nxt)[32] = (g & 1) ? va : vb;
+    if constexpr (g + 1 < NG) {
+      tmem_ld32(addr(g + 1), nxt);
+      tmem_pin32(cur);
+    }
+    if constexpr (g + 1 == NG) done.issue();
+    f(gg, cur);
+    if constexpr (g + 1 < NG) tmem_wait32(nxt);
+    if constexpr (g + 1 == NG) done.finish();
+  });
+}
+
 // Requantise 32 accumulators of one row -> int8 -> panel buffer (and/or global).
 //   panel      shared-memory panel buffer of a [kS x *] matrix (nullptr: do not store to smem)
 //   col        first of the 32 columns inside that matrix
@@ -626,6 +646,10 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
                  for (int i = 0; i < 32; ++i) amax = max(amax, (int)v[i]);
                },
                NoRelease{});
+#ifndef ITA_NO_PRELOAD
+  uint32_t pre[32];                               // group 0 of the next pass, in flight while the row partners exchange
+  tmem_ld32(addr(0), pre);
+#endif
   amax = xchg_max<NPART>(pc, HALF, row, amax);
   const int zmax = rq_off_bits<MODE>((uint32_t)amax, rq);
   const int mp = min(max(zmax, 0), 255);          // m + 128
@@ -693,7 +717,11 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
         d1 = (uint32_t)max((int)d1, dmin);
       }
     };
+#ifndef ITA_NO_PRELOAD
+    tmem_walk_pre<2>(pre, addr,
+#else
     tmem_walk<2>(addr,
+#endif
                  [&](auto, const uint32_t(&v)[32]) {
 #pragma unroll
                    for (int i = 0; i < 32; i += 2) {
@@ -703,9 +731,16 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
                    }
                  },
                  NoRelease{});
+#ifndef ITA_NO_PRELOAD
+    tmem_ld32(addr(0), pre);
+#endif
     sum = xchg_sum<NPART>(pc, HALF, row, sum);
     const uint32_t inv8 = ((((255u * 65536u) / sum) >> 8) << 1) << odd;
+#ifndef ITA_NO_PRELOAD
+    tmem_walk_pre<2>(pre, addr,
+#else
     tmem_walk<2>(addr,
+#endif
                  [&](auto gg, const uint32_t(&v)[32]) {
                    constexpr int g = decltype(gg)::value;
 #pragma unroll
@@ -728,15 +763,26 @@ __device__ __forceinline__ void itamax_repo_half_fp(bool allow_fast, int HALF, u
     else passes(std::false_type{});
   } else {
     auto dist = [&](uint32_t v) -> uint32_t { return (uint32_t)(mp - min(max(rq_off_bits<MODE>(v, rq), 0), 255)); };
+#ifndef ITA_NO_PRELOAD
+    tmem_walk_pre<2>(pre, addr,
+#else
     tmem_walk<2>(addr,
+#endif
                  [&](auto, const uint32_t(&v)[32]) {
 #pragma unroll
                    for (int i = 0; i < 32; ++i) sum += shr_clamp(256u, dist(v[i]));
                  },
                  NoRelease{});
+#ifndef ITA_NO_PRELOAD
+    tmem_ld32(addr(0), pre);
+#endif
     sum = xchg_sum<NPART>(pc, HALF, row, sum);
     const uint32_t inv8 = ((255u * 65536u) / sum) >> 8;
+#ifndef ITA_NO_PRELOAD
+    tmem_walk_pre<2>(pre, addr,
+#else
     tmem_walk<2>(addr,
+#endif
                  [&](auto gg, const uint32_t(&v)[32]) {
                    constexpr int g = decltype(gg)::value;
 #pragma unroll

@@ -609,6 +609,30 @@ def test_fusion_conv_kernel_vs_torch_fp32(ita, E):
     assert d <= 5e-5, d
 
 
+def test_lstm_cell_kernel_vs_torch_lstm(ita):
+    """``ita_lstm_cell_forward`` behind two cuBLAS gate GEMMs == one time step of ``torch.nn.LSTM`` (3 layers, 517 -> 128, the
+    model's head, reference QAT/model.py:68,128) on the GPU; fp32, tolerance 2e-6 (expf / tanhf vs ATen's kernels)."""
+    L = ita._lib
+    torch.manual_seed(3)
+    B, I, Hd, NL = 53, 517, 128, 3
+    lstm = torch.nn.LSTM(input_size=I, hidden_size=Hd, num_layers=NL).to(_dev()).eval()
+    x = torch.randn(1, B, I, device=_dev())
+    h0, c0 = torch.randn(NL, B, Hd, device=_dev()) * 0.5, torch.randn(NL, B, Hd, device=_dev()) * 0.5
+    with torch.no_grad():
+        ref, (hr, cr) = lstm(x, (h0, c0))
+        xs = x[0]
+        hn, cn = torch.empty_like(h0), torch.empty_like(c0)
+        for l in range(NL):
+            gates = torch.addmm(getattr(lstm, f"bias_ih_l{l}") + getattr(lstm, f"bias_hh_l{l}"), xs, getattr(lstm, f"weight_ih_l{l}").t())
+            gates.addmm_(h0[l], getattr(lstm, f"weight_hh_l{l}").t())
+            L.check(L.load().ita_lstm_cell_forward(gates.data_ptr(), c0[l].contiguous().data_ptr(), hn[l].data_ptr(), cn[l].data_ptr(), B, Hd,
+                                                   torch.cuda.current_stream().cuda_stream), "ita_lstm_cell_forward")
+            xs = hn[l]
+    torch.cuda.synchronize()
+    assert (hn - hr).abs().max().item() <= 2e-6 and (cn - cr).abs().max().item() <= 2e-6, ((hn - hr).abs().max().item(), (cn - cr).abs().max().item())
+    assert (xs - ref[0]).abs().max().item() <= 2e-6
+
+
 # ----------------------------------------------------------------------------------------------------- full-size properties
 def test_full_size_properties(ita, R, RC):
     """BASELINE configs[1] size (4096 frames): fused == staged on every frame, permutation equivariance, duplicate
