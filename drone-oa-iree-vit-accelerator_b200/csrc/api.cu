@@ -303,25 +303,37 @@ static int forward_host_impl(ita_mha_handle *h, const int8_t *x_host, int8_t *y_
     ITA_CUDA_TRY(cudaStreamWaitEvent(h->aux[1], h->ev_start, 0));
   }
   rc = ITA_OK;
+  // inside the loop a CUDA error must not return before the helper streams are joined back into `s` below
+#define ITA_CUDA_STEP(expr)                                                                                \
+  {                                                                                                        \
+    cudaError_t _e = (expr);                                                                               \
+    if (_e != cudaSuccess) {                                                                               \
+      set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));                     \
+      rc = ITA_ERR_CUDA;                                                                                   \
+      break;                                                                                               \
+    }                                                                                                      \
+  }
   for (int64_t c = 0; c < nchunk && !rc; ++c) {
     const int64_t b0 = c * per, nb = (b0 + per <= batch) ? per : batch - b0;
     if (nb <= 0) break;
     if (nchunk == 1) {
-      ITA_CUDA_TRY(cudaMemcpyAsync(xd, x_host, frame * nb, cudaMemcpyHostToDevice, s));
+      ITA_CUDA_STEP(cudaMemcpyAsync(xd, x_host, frame * nb, cudaMemcpyHostToDevice, s));
       rc = forward_dev(h, xd, yd, nb, path, s);
-      if (!rc) ITA_CUDA_TRY(cudaMemcpyAsync(y_host, yd, frame * nb, cudaMemcpyDeviceToHost, s));
+      if (rc) break;
+      ITA_CUDA_STEP(cudaMemcpyAsync(y_host, yd, frame * nb, cudaMemcpyDeviceToHost, s));
     } else {
       // aux[0]: H2D copies, s: kernels, aux[1]: D2H copies
-      ITA_CUDA_TRY(cudaMemcpyAsync(xd + frame * b0, x_host + frame * b0, frame * nb, cudaMemcpyHostToDevice, h->aux[0]));
-      ITA_CUDA_TRY(cudaEventRecord(h->ev_in[c], h->aux[0]));
-      ITA_CUDA_TRY(cudaStreamWaitEvent(s, h->ev_in[c], 0));
+      ITA_CUDA_STEP(cudaMemcpyAsync(xd + frame * b0, x_host + frame * b0, frame * nb, cudaMemcpyHostToDevice, h->aux[0]));
+      ITA_CUDA_STEP(cudaEventRecord(h->ev_in[c], h->aux[0]));
+      ITA_CUDA_STEP(cudaStreamWaitEvent(s, h->ev_in[c], 0));
       rc = forward_dev(h, xd + frame * b0, yd + frame * b0, nb, path, s);
       if (rc) break;
-      ITA_CUDA_TRY(cudaEventRecord(h->ev_k[c], s));
-      ITA_CUDA_TRY(cudaStreamWaitEvent(h->aux[1], h->ev_k[c], 0));
-      ITA_CUDA_TRY(cudaMemcpyAsync(y_host + frame * b0, yd + frame * b0, frame * nb, cudaMemcpyDeviceToHost, h->aux[1]));
+      ITA_CUDA_STEP(cudaEventRecord(h->ev_k[c], s));
+      ITA_CUDA_STEP(cudaStreamWaitEvent(h->aux[1], h->ev_k[c], 0));
+      ITA_CUDA_STEP(cudaMemcpyAsync(y_host + frame * b0, yd + frame * b0, frame * nb, cudaMemcpyDeviceToHost, h->aux[1]));
     }
   }
+#undef ITA_CUDA_STEP
   if (nchunk > 1) {
     // join the helper streams back into `s`
     cudaEventRecord(h->ev_done[0], h->aux[0]);

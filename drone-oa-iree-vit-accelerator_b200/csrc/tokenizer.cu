@@ -5,7 +5,8 @@
 // uint8 image by 1/255) and the int8 token tile [128, E] the attention kernel consumes is produced without a float
 // round trip through Python.
 //
-// One CTA per frame, one thread per token.  The resize is linear and so is the convolution, so a token is
+// One CTA per frame; a thread blends one token's patch, then owns 4 tokens x E/4 channels of the product.  The resize is linear
+// and so is the convolution, so a token is
 //     bias + W[E x 49] . patch,   patch[ky,kx] = sum over the 4 bilinear taps of weight_tap * image[2*ty + ky - 3, 2*tx + kx - 3]
 // (zero padding): 4*49 blends + 49*E FMAs per token instead of 4*49*E (only 512 of the 1350 conv pixels are ever sampled and
 // none is shared between tokens).  The summation order differs from conv-then-resize by float rounding only (1e-6 relative;
@@ -15,19 +16,21 @@
 namespace ita {
 
 constexpr int kImgH = 60, kImgW = 90, kConvH = 30, kConvW = 45, kTokH = 8, kTokW = 16, kTaps = 49;
+constexpr int kTokBuf = kImgH * kImgW > kTaps * 128 ? kImgH * kImgW : kTaps * 128;   // floats
 
 template <int E, bool U8>
 __global__ void __launch_bounds__(128) k_tokenize(const void *__restrict__ img, const float *__restrict__ w, const float *__restrict__ cb,
                                                   const float *__restrict__ gamma, const float *__restrict__ beta, float eps,
                                                   float *__restrict__ tok, int8_t *__restrict__ tokq, float inv_q) {
-  __shared__ __align__(16) float s_img[kImgH * kImgW];
-  __shared__ __align__(16) float s_w[kTaps * E];          // transposed: [tap][channel]
+  extern __shared__ __align__(16) float tk_smem[];
+  float *s_img = tk_smem;                                 // the frame (5400 floats), later the blended patches [49][128]
+  float *s_w = tk_smem + kTokBuf;                         // transposed: [tap][channel]
+  float *s_lut = s_w + kTaps * E;                         // u8 -> f32(u8) / 255 (U8 only)
   const long long f = blockIdx.x;
   const int t = threadIdx.x;
   if constexpr (U8) {
     // u8 / 255.0f (a true division, as main.cpp:168) has 256 possible results: a table per CTA instead of 5400 divisions;
     // the frame is read as 16-byte words (5400 = 337 * 16 + 8)
-    __shared__ float s_lut[256];
     for (int i = t; i < 256; i += 128) s_lut[i] = __fdiv_rn((float)i, 255.0f);
     __syncthreads();
     const uint8_t *src = reinterpret_cast<const uint8_t *>(img) + f * (kImgH * kImgW);
@@ -78,46 +81,77 @@ __global__ void __launch_bounds__(128) k_tokenize(const void *__restrict__ img, 
       }
     }
   }
-  // ---- W . patch + bias
-  float acc[E];
+  // ---- the blended patches go through shared memory ([tap][token]), so that the [128 x 49] . [49 x E] product can be register
+  //      tiled: a thread owns 4 tokens x E/4 channels and every shared-memory load feeds 8-16 FMAs (one token x all channels per
+  //      thread, the first version, was bound by the weight broadcasts: 4 FMAs per LDS.128)
+  float *s_patch = s_img;                          // the image is dead once every thread has blended its patch
+  __syncthreads();
 #pragma unroll
-  for (int c = 0; c < E; ++c) acc[c] = cb[c];
+  for (int k = 0; k < kTaps; ++k) s_patch[k * 128 + t] = patch[k];
+  __syncthreads();
+  constexpr int CG = E / 4;                        // channels per thread; lane = 4 * token group + channel group
+  const int tg = t >> 2, cg = t & 3;               // tokens 4 tg .. 4 tg + 3, channels cg * CG .. + CG
+  float acc[4][CG];
 #pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int c = 0; c < CG; ++c) acc[q][c] = cb[cg * CG + c];
+#pragma unroll 7
   for (int k = 0; k < kTaps; ++k) {
-    const float4 *wr = reinterpret_cast<const float4 *>(s_w + k * E);
+    const float4 pv = *reinterpret_cast<const float4 *>(s_patch + k * 128 + tg * 4);
+    const float pq[4] = {pv.x, pv.y, pv.z, pv.w};
+    const float4 *wr = reinterpret_cast<const float4 *>(s_w + k * E + cg * CG);
 #pragma unroll
-    for (int c4 = 0; c4 < E / 4; ++c4) {
-      const float4 ww = wr[c4];                    // same address in every thread: a shared-memory broadcast
-      acc[c4 * 4 + 0] = fmaf(ww.x, patch[k], acc[c4 * 4 + 0]);
-      acc[c4 * 4 + 1] = fmaf(ww.y, patch[k], acc[c4 * 4 + 1]);
-      acc[c4 * 4 + 2] = fmaf(ww.z, patch[k], acc[c4 * 4 + 2]);
-      acc[c4 * 4 + 3] = fmaf(ww.w, patch[k], acc[c4 * 4 + 3]);
+    for (int c4 = 0; c4 < CG / 4; ++c4) {
+      const float4 ww = wr[c4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        acc[q][c4 * 4 + 0] = fmaf(ww.x, pq[q], acc[q][c4 * 4 + 0]);
+        acc[q][c4 * 4 + 1] = fmaf(ww.y, pq[q], acc[q][c4 * 4 + 1]);
+        acc[q][c4 * 4 + 2] = fmaf(ww.z, pq[q], acc[q][c4 * 4 + 2]);
+        acc[q][c4 * 4 + 3] = fmaf(ww.w, pq[q], acc[q][c4 * 4 + 3]);
+      }
     }
   }
-  // ---- LayerNorm over the E channels of the token (biased variance), then the quant stub
-  float s = 0.f;
+  // ---- LayerNorm over the E channels of a token (biased variance; the four channel groups of a token are adjacent lanes),
+  //      then the quant stub
+  float gm[CG], bt[CG];
 #pragma unroll
-  for (int c = 0; c < E; ++c) s += acc[c];
-  const float mean = s * (1.0f / E);
-  float ss = 0.f;
+  for (int c = 0; c < CG; ++c) {
+    gm[c] = gamma[cg * CG + c];
+    bt[c] = beta[cg * CG + c];
+  }
 #pragma unroll
-  for (int c = 0; c < E; ++c) ss += (acc[c] - mean) * (acc[c] - mean);
-  const float rstd = 1.0f / sqrtf(ss * (1.0f / E) + eps);
-  float *to = tok ? tok + (f * (kTokH * kTokW) + t) * (long long)E : nullptr;
-  int8_t *tq = tokq ? tokq + (f * (kTokH * kTokW) + t) * (long long)E : nullptr;
+  for (int q = 0; q < 4; ++q) {
+    float sm_ = 0.f;
 #pragma unroll
-  for (int c4 = 0; c4 < E / 4; ++c4) {
-    float o[4];
+    for (int c = 0; c < CG; ++c) sm_ += acc[q][c];
+    sm_ += __shfl_xor_sync(0xffffffffu, sm_, 1);
+    sm_ += __shfl_xor_sync(0xffffffffu, sm_, 2);
+    const float mean = sm_ * (1.0f / E);
+    float ss = 0.f;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) o[i] = (acc[c4 * 4 + i] - mean) * rstd * gamma[c4 * 4 + i] + beta[c4 * 4 + i];
-    if (to) reinterpret_cast<float4 *>(to)[c4] = make_float4(o[0], o[1], o[2], o[3]);
-    if (tq) {
-      char4 q;
-      q.x = (int8_t)(int)fminf(fmaxf(nearbyintf(o[0] * inv_q), -128.f), 127.f);
-      q.y = (int8_t)(int)fminf(fmaxf(nearbyintf(o[1] * inv_q), -128.f), 127.f);
-      q.z = (int8_t)(int)fminf(fmaxf(nearbyintf(o[2] * inv_q), -128.f), 127.f);
-      q.w = (int8_t)(int)fminf(fmaxf(nearbyintf(o[3] * inv_q), -128.f), 127.f);
-      reinterpret_cast<char4 *>(tq)[c4] = q;
+    for (int c = 0; c < CG; ++c) ss += (acc[q][c] - mean) * (acc[q][c] - mean);
+    ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+    ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+    const float rstd = 1.0f / sqrtf(ss * (1.0f / E) + eps);
+    const long long row = f * (kTokH * kTokW) + tg * 4 + q;
+    float *to = tok ? tok + row * (long long)E + cg * CG : nullptr;
+    int8_t *tq = tokq ? tokq + row * (long long)E + cg * CG : nullptr;
+#pragma unroll
+    for (int c4 = 0; c4 < CG / 4; ++c4) {
+      float o[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[i] = (acc[q][c4 * 4 + i] - mean) * rstd * gm[c4 * 4 + i] + bt[c4 * 4 + i];
+      if (to) reinterpret_cast<float4 *>(to)[c4] = make_float4(o[0], o[1], o[2], o[3]);
+      if (tq) {
+        char4 qv;
+        qv.x = (int8_t)(int)fminf(fmaxf(nearbyintf(o[0] * inv_q), -128.f), 127.f);
+        qv.y = (int8_t)(int)fminf(fmaxf(nearbyintf(o[1] * inv_q), -128.f), 127.f);
+        qv.z = (int8_t)(int)fminf(fmaxf(nearbyintf(o[2] * inv_q), -128.f), 127.f);
+        qv.w = (int8_t)(int)fminf(fmaxf(nearbyintf(o[3] * inv_q), -128.f), 127.f);
+        reinterpret_cast<char4 *>(tq)[c4] = qv;
+      }
     }
   }
 }
@@ -139,12 +173,26 @@ int launch_tokenizer(const void *img, int is_u8, int64_t B, int E, const float *
   }
   const float inv = tokq ? 1.0f / q_scale : 0.f;          // formed in fp32 like ATen's quantize_per_tensor
   const unsigned grid = (unsigned)B;
+  const size_t smem = sizeof(float) * ((size_t)kTokBuf + (size_t)kTaps * E + 256);
+  if (smem > 48 * 1024) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t e1 = cudaFuncSetAttribute((const void *)k_tokenize<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaError_t e2 = cudaFuncSetAttribute((const void *)k_tokenize<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e1 != cudaSuccess || e2 != cudaSuccess) {
+        cudaGetLastError();
+        set_error("tokenizer: cudaFuncSetAttribute(%zu B shared memory) failed", smem);
+        return ITA_ERR_CUDA;
+      }
+      attr_set = true;
+    }
+  }
   if (E == 64) {
-    if (is_u8) k_tokenize<64, true><<<grid, 128, 0, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
-    else k_tokenize<64, false><<<grid, 128, 0, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
+    if (is_u8) k_tokenize<64, true><<<grid, 128, smem, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
+    else k_tokenize<64, false><<<grid, 128, smem, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
   } else {
-    if (is_u8) k_tokenize<128, true><<<grid, 128, 0, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
-    else k_tokenize<128, false><<<grid, 128, 0, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
+    if (is_u8) k_tokenize<128, true><<<grid, 128, smem, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
+    else k_tokenize<128, false><<<grid, 128, smem, s>>>(img, w, cb, gamma, beta, eps, tok, tokq, inv);
   }
   count_launch();
   ITA_CUDA_TRY(cudaGetLastError());
