@@ -10,13 +10,13 @@
 // Why two kernels: tensor memory.  A logits tile of one row tile is 128 lanes x 256 columns (half the SM's 512 columns) and
 // has to stay resident for the three ITAmax passes; accumulating the output projection across heads in TMEM would take the
 // other 256 columns (2 row tiles x 128), leaving nothing for the projections and A.V.  The context is 64 KB per frame and
-// is re-read by the second kernel from L2/HBM (k_ita_mh_out: 13 % of the step at config 3).
+// is re-read by the second kernel from L2/HBM (8 % of k_ita_mh's own time at config 3).
 //
 // k_ita_mh, one CTA per SM, frames strided over CTAs, an "item" = (frame, head):
 //   shared memory   X [256 x E] (whole frame), Q [256 x P], K and V [256 x P] double-buffered (the next head's projections
 //                   run while this head's attention is in progress), Asm [128 x 256] u8 (one row tile), per-head weight
-//                   block [Wq | Wk | Wv]^T with the digit K columns, double-buffered and streamed from L2 (30 KB per head),
-//                   every head's offset tiles and stage constants and the constant digit A tile resident.  All operands in the no-swizzle panel layout of
+//                   block [Wq | Wk | Wv]^T with the digit K columns + the head's offset tiles, double-buffered and streamed
+//                   from L2 (30 KB per head), the constant digit A tile.  All operands in the no-swizzle panel layout of
 //                   fused_kernel.cuh, with 256-row panels for X/Q/K/V.
 //   tensor memory   RS = 256 columns (logits tile), RP = 192 (Q | K | V projection accumulators of one row tile), RA = 64
 //                   (context chunk)
