@@ -467,6 +467,32 @@ def test_module_surface(ita, R):
     assert ita.quantize(v, s).cpu().tolist() == [0, 2, 0, -2, 2, 127, -128, 0]
 
 
+def test_module_multi_head_runs_the_tcgen05_kernels(ita, R):
+    """``ITASelfAttention(embed_dim=128, proj_dim=256, num_heads=4)`` on 256 tokens (the module form of BASELINE config 3: heads
+    are column slices of one projection, contexts concatenated into one out_proj, reference layers.py:82,106-123) takes the
+    multi-head tcgen05 kernels and equals the oracle's torch head convention bit-exactly."""
+    import bench
+    g = np.random.default_rng(17)
+    m = ita.ITASelfAttention(128, 256, 4)
+    for name, (n_out, n_in) in (("q_proj", (256, 128)), ("k_proj", (256, 128)), ("v_proj", (256, 128)), ("out_proj", (128, 256))):
+        lin = getattr(m, name)
+        lin.weight_int8.copy_(torch.from_numpy(np.clip(np.rint(g.normal(0, 32, (n_out, n_in))), -128, 127).astype(np.int8)))
+        lin.weight_scale = 0.004
+        lin.bias.copy_(torch.from_numpy(g.normal(0, 0.3, n_out).astype(np.float32)))
+    m.quant.scale, m.q_proj.scale, m.k_proj.scale, m.v_proj.scale = 0.03, 0.06, 0.06, 0.05
+    m.matmul1.scale, m.matmul2.scale, m.out_proj.scale = 0.9, 0.02, 0.05
+    p = m.quant_params(256)
+    assert p.H == 4 and p.P == 64 and p.head_mode == ita._lib.HEADS_TORCH
+    eng = m.engine(256, _dev())
+    assert eng.fused_supported and "k_ita_mh" in eng.describe(), eng.describe()
+    X = R.make_input(3, 256, 128, seed=8)
+    y = m.forward_int8(torch.from_numpy(X).to(_dev()))
+    eng.sync_check()
+    _cmp(y, R.mha_forward(bench.to_oracle(R, p), X)["Y"], "multi-head module vs oracle (torch head convention)")
+    yf = m(torch.from_numpy(X.astype(np.float32) * np.float32(0.03)).to(_dev()))
+    assert np.array_equal(yf.cpu().numpy(), y.cpu().numpy().astype(np.float32) * np.float32(0.05))
+
+
 def test_module_hooks_fire_with_quantised_stage_tensors(ita, R):
     """Forward hooks on the named submodules (the way tests/export_and_validation_W_B.py:186-205 captures a block) receive
     quantised tensors with the reference's shapes, scales and integer values; registering hooks does not change the output."""
