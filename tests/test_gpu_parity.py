@@ -663,6 +663,33 @@ def test_lstm_cell_kernel_vs_torch_lstm(ita):
     assert (xs - ref[0]).abs().max().item() <= 1e-5
 
 
+def test_graphed_model_step_equals_eager(ita, R):
+    """``GraphedStep`` (one ITAViTLSTM step captured in a CUDA graph, LSTM state carried inside) reproduces the eager forward
+    over three consecutive steps of a 5-drone batch, bit for bit (the graph replays the same kernels)."""
+    import importlib
+    import seeded
+    M = importlib.import_module("drone-oa-iree-vit-accelerator_b200.model")
+    sd = dict(torch.load(os.path.join(GOLDEN, "qat_state_E64.pt"), weights_only=False))
+    for name, shape in M.reference_float_shapes(1, 64).items():
+        sd[name] = torch.from_numpy(seeded.float_param(name, shape))
+    m = M.ITAViTLSTM.from_state_dict(sd).to(_dev())
+    g = torch.Generator().manual_seed(4)
+    B = 5
+    step = M.GraphedStep(m, B, _dev())
+    hidden = None
+    for k in range(3):
+        img = torch.randint(0, 256, (B, 60, 90), generator=g, dtype=torch.uint8).to(_dev())
+        vel = (torch.rand((B, 1), generator=g) * 5).to(_dev())
+        quat = torch.rand((B, 4), generator=g).to(_dev())
+        want, hidden = m([img, vel, quat] + ([hidden] if hidden is not None else []))
+        got = step(img, vel, quat)
+        torch.cuda.synchronize()
+        assert torch.equal(got, want), (k, (got - want).abs().max().item())
+    assert torch.equal(step.h, hidden[0]) and torch.equal(step.c, hidden[1])
+    step.reset_state()
+    assert float(step.h.abs().max()) == 0.0
+
+
 # ----------------------------------------------------------------------------------------------------- full-size properties
 def test_full_size_properties(ita, R, RC):
     """BASELINE configs[1] size (4096 frames): fused == staged on every frame, permutation equivariance, duplicate
