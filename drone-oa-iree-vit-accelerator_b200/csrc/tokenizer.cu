@@ -175,7 +175,10 @@ int launch_tokenizer(const void *img, int is_u8, int64_t B, int E, const float *
   const unsigned grid = (unsigned)B;
   const size_t smem = sizeof(float) * ((size_t)kTokBuf + (size_t)kTaps * E + 256);
   if (smem > 48 * 1024) {
-    static bool attr_set = false;
+    static bool attr_done[64] = {};                      // function attributes are per device
+    int dev = 0;
+    ITA_CUDA_TRY(cudaGetDevice(&dev));
+    bool &attr_set = attr_done[dev & 63];
     if (!attr_set) {
       cudaError_t e1 = cudaFuncSetAttribute((const void *)k_tokenize<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       cudaError_t e2 = cudaFuncSetAttribute((const void *)k_tokenize<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -344,7 +347,10 @@ int launch_fuse_conv(const float *x, int64_t B, int E, const float *w, const flo
   }
   const int cin = E / 4 + E;
   const size_t smem = sizeof(float) * ((size_t)E * kFuTokPad + (size_t)kFuChunk * kFuMapCh + (size_t)cin * 9 * kFuWPad);
-  static bool attr_set[2] = {false, false};
+  static bool attr_done[64][2] = {};                     // function attributes are per device
+  int dev = 0;
+  ITA_CUDA_TRY(cudaGetDevice(&dev));
+  bool *attr_set = attr_done[dev & 63];
   const int which = E == 64 ? 0 : 1;
   if (!attr_set[which]) {
     cudaError_t e = E == 64 ? cudaFuncSetAttribute((const void *)k_fuse_conv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
