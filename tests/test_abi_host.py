@@ -236,3 +236,28 @@ def test_full_model_state_dict_reader_and_float_stages(ita):
         assert np.abs(out.numpy() - q["out"]).max() <= 1e-6 and np.abs(h.numpy() - q["hn"]).max() <= 1e-6
     with pytest.raises(ValueError):
         m([torch.zeros(1, 1, 60, 90), torch.zeros(1, 1), torch.zeros(1, 4)])     # CPU tensors: no CPU fallback
+
+
+def test_committed_bench_lines_follow_the_contract():
+    """The bench lines committed under profiles/ (taken on the B200 box with the final build) carry every key of the bench
+    contract: the driver parses the same line from ``python bench.py``."""
+    import json
+    prof = os.path.join(ROOT, "profiles")
+    for name in ("bench_r2_final_c2.json", "bench_r2_final_c3.json", "bench_r2_final_c4.json"):
+        d = json.load(open(os.path.join(prof, name)))
+        for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                  "dtype", "data", "config", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks"):
+            assert k in d, (name, k)
+        assert d["unit"] == "frames/s" and d["higher_is_better"] is True and d["scaling"] == "weak" and d["vs_baseline"] is None
+        assert "workload" in d["config"] and d["config"]["rounding"] == "torch_rne_f32"
+        for k in ("bound", "achieved", "peak", "unit", "frac", "traffic"):
+            assert k in d["roofline"], (name, k)
+        for k in ("value", "unit", "cores", "kind", "sample"):
+            assert k in d["cpu_baseline"], (name, k)
+        for k in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step"):
+            assert k in d["e2e"], (name, k)
+        assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["gpu_launches"] > 0 and d["parity_spot_check"] is True
+        assert d["clocks"]["reasons"] == [] or d["clocks"]["reasons"] == ["sw_power_cap"]
+    ref = json.load(open(os.path.join(prof, "bench_r2_final_c2_reference_arm.json")))
+    assert ref["impl"] == "reference" and ref["e2e"]["h2d_bytes_per_step"] == 0 and ref["cpu_baseline"]["kind"] == "port"
+    assert ref["config"]["frames_per_gpu_per_step"] == json.load(open(os.path.join(prof, "bench_r2_final_c2.json")))["config"]["frames_per_gpu_per_step"]

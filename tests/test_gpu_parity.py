@@ -757,6 +757,35 @@ def test_multi_head_every_intermediate_vs_oracle(ita, R, round_mode, softmax_mod
     eng.close()
 
 
+def test_multi_head_limits_and_fallbacks(ita, R, RC):
+    """Edges of the multi-head tcgen05 path: 8 heads with the concatenated convention run on it; 8 heads with per-head
+    accumulators do not fit tensor memory (H * E / 2 > 256 columns) and take the staged kernels -- reported, and still bit-exact;
+    an empty batch is a no-op; E != 128 at S = 256 is staged."""
+    X = R.make_input(2, 256, 128, seed=3)
+    p8 = R.make_synthetic(256, 128, 64, 8, seed=21, head_mode=1)
+    eng = _engine(ita, p8)
+    assert eng.fused_supported and "k_ita_mh" in eng.describe()
+    y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
+    eng.sync_check()
+    _cmp(y, RC.mha(p8, X, intermediates=False)["Y"], "8 heads, concatenated")
+    assert tuple(eng.forward(torch.empty((0, 256, 128), dtype=torch.int8, device=_dev())).shape) == (0, 256, 128)
+    eng.close()
+    p8p = R.make_synthetic(256, 128, 64, 8, seed=21, head_mode=0)
+    eng = _engine(ita, p8p)
+    assert not eng.fused_supported and "tensor-memory" in eng.fused_unsupported_reason()
+    y = eng.forward(torch.from_numpy(X).to(_dev()))                     # PATH_AUTO -> staged (says so once on stderr)
+    _cmp(y, RC.mha(p8p, X, intermediates=False)["Y"], "8 heads, per-head convention (staged)")
+    with pytest.raises(ita.ITAError):
+        eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
+    eng.close()
+    p64 = R.make_synthetic(256, 64, 64, 2, seed=5, head_mode=1)
+    eng = _engine(ita, p64)
+    assert not eng.fused_supported
+    X64 = R.make_input(2, 256, 64, seed=4)
+    _cmp(eng.forward(torch.from_numpy(X64).to(_dev())), RC.mha(p64, X64, intermediates=False)["Y"], "S=256, E=64 (staged)")
+    eng.close()
+
+
 @pytest.mark.parametrize("fp", ["2", "1", "0"])
 def test_multi_head_requant_forms_and_batches(ita, R, RC, fp, monkeypatch):
     """The multi-head kernels in every requant form (ITA_FUSED_FP: 2 = two-FFMA / one-FFMA offset forms, 1 = three-FFMA, 0 =
