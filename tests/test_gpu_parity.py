@@ -758,17 +758,20 @@ def test_multi_head_every_intermediate_vs_oracle(ita, R, round_mode, softmax_mod
 
 
 def test_multi_head_limits_and_fallbacks(ita, R, RC):
-    """Edges of the multi-head tcgen05 path: 8 heads with the concatenated convention run on it; 8 heads with per-head
-    accumulators do not fit tensor memory (H * E / 2 > 256 columns) and take the staged kernels -- reported, and still bit-exact;
-    an empty batch is a no-op; E != 128 at S = 256 is staged."""
+    """Edges of the multi-head tcgen05 path: an empty batch is a no-op; 8 heads exceed what k_ita_mh_out keeps on chip (three
+    context tiles of H * P columns in shared memory; per-head accumulators H * E / 2 > 256 tensor-memory columns) and take the
+    staged kernels -- reported, and still bit-exact; E != 128 at S = 256 is staged."""
     X = R.make_input(2, 256, 128, seed=3)
+    p4 = R.make_synthetic(256, 128, 64, 4, seed=21, head_mode=1)
+    eng = _engine(ita, p4)
+    assert eng.fused_supported and "k_ita_mh" in eng.describe()
+    assert tuple(eng.forward(torch.empty((0, 256, 128), dtype=torch.int8, device=_dev())).shape) == (0, 256, 128)
+    eng.close()
     p8 = R.make_synthetic(256, 128, 64, 8, seed=21, head_mode=1)
     eng = _engine(ita, p8)
-    assert eng.fused_supported and "k_ita_mh" in eng.describe()
-    y = eng.forward(torch.from_numpy(X).to(_dev()), path=ita.PATH_FUSED)
-    eng.sync_check()
-    _cmp(y, RC.mha(p8, X, intermediates=False)["Y"], "8 heads, concatenated")
-    assert tuple(eng.forward(torch.empty((0, 256, 128), dtype=torch.int8, device=_dev())).shape) == (0, 256, 128)
+    assert not eng.fused_supported and "shared memory" in eng.fused_unsupported_reason(), eng.fused_unsupported_reason()
+    y = eng.forward(torch.from_numpy(X).to(_dev()))                     # PATH_AUTO -> staged (says so once on stderr)
+    _cmp(y, RC.mha(p8, X, intermediates=False)["Y"], "8 heads, concatenated (staged)")
     eng.close()
     p8p = R.make_synthetic(256, 128, 64, 8, seed=21, head_mode=0)
     eng = _engine(ita, p8p)
