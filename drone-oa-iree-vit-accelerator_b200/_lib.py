@@ -21,6 +21,7 @@ ST_Q, ST_K, ST_V, ST_QK, ST_AV, ST_O, ST_SUM, ST_FC1, ST_RELU, ST_FC2 = range(10
 NUM_STAGES = 10
 STEP1_QP, STEP2_KP, STEP3_VP, STEP4_QK, STEP4_SOFTMAX, STEP5_AV, STEP6_O, STEP7_OSUM = 1, 2, 3, 4, 40, 5, 6, 7
 PATH_AUTO, PATH_FUSED, PATH_STAGED = 0, 1, 2
+LAYER_STATIC_SCRATCH_BYTES = 16 * 1024 * 1024   # ITA_LAYER_STATIC_SCRATCH_BYTES
 
 _i8p, _u8p, _i32p, _f32p = C.POINTER(C.c_int8), C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_float)
 
@@ -66,6 +67,7 @@ SYMBOLS = {
     "ita_residual_layernorm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p,
                                          C.c_void_p, C.c_float, C.c_int64, C.c_int32, C.c_void_p]),
     "ita_encoder_layer_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "ita_encoder_layer_forward_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "ita_tokenizer_forward": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
                                         C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]),
     "ita_fusion_conv_forward": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -232,6 +232,30 @@ class ITAEngine:
         return y
 
 
+    @property
+    def layer_static_max_batch(self) -> int:
+        """Largest batch ``layer_static`` accepts for this handle's S and E (ITA_LAYER_STATIC_SCRATCH_BYTES / (8*S*E))."""
+        return L.LAYER_STATIC_SCRATCH_BYTES // (8 * self.S * self.E)
+
+    def layer_static(self, x: torch.Tensor, lp, out: torch.Tensor, stream: Optional[torch.cuda.Stream] = None):
+        """``layer()`` for a caller that must not allocate device memory at call time (a real-time loop, a host whose memory
+        pool is already handed out): the C call keeps its intermediates in a fixed 16 MiB array inside the library and
+        performs no cudaMalloc / cudaFree, and this wrapper creates no tensor either, so ``out`` (f32 cuda [B,S,E]) is
+        mandatory.  Bit-identical to ``layer()``.  Limits: ``B <= layer_static_max_batch``; single-head handles on the
+        fused tcgen05 kernels only; one array per GPU shared by every call, so calls that could overlap on the GPU must be
+        ordered (one stream); first call on a device belongs to start-up.  See include/ita_b200.h."""
+        for t, name in ((x, "x"), (out, "out")):
+            if t.dtype != torch.float32 or not t.is_cuda or not t.is_contiguous() or t.dim() != 3 or \
+                    tuple(t.shape[1:]) != (self.S, self.E):
+                raise ValueError(f"layer_static() expects {name} as a contiguous float32 cuda tensor [B,{self.S},{self.E}]")
+        if out.shape[0] != x.shape[0]:
+            raise ValueError("layer_static(): x and out differ in batch")
+        L.check(self.lib.ita_encoder_layer_forward_static(self._h, C.byref(lp), C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()),
+                                                          int(x.shape[0]), _stream_ptr(stream, self.device)),
+                "ita_encoder_layer_forward_static")
+        return out
+
+
 def quantize(x: torch.Tensor, scale: float) -> torch.Tensor:
     """QuantStub of the operator boundary (reference models/ITA/QAT/layers.py:103): sat8(rne(x / scale))."""
     if not x.is_cuda or x.dtype != torch.float32:

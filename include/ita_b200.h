@@ -190,6 +190,27 @@ typedef struct ita_layer_params {
 ITA_API int ita_encoder_layer_forward(ita_mha_handle *h, const ita_layer_params *lp, const float *x_dev, float *y_dev, int64_t batch,
                                       void *cuda_stream);
 
+/* ita_encoder_layer_forward for callers that must not allocate.  It has NO counterpart in the reference (the reference's
+ * layer runs inside torch / IREE, which own their memory); it exists for hosts of this library that cannot let a dispatch
+ * call cudaMalloc: the drone's per-packet inference loop (cudaMalloc / cudaFree stall the whole device and would land inside
+ * the control period), a runtime that has already handed out all device memory from its own pool, code running inside
+ * another component's stream-ordered region.  Same arguments, same five kernels and bit-identical results as
+ * ita_encoder_layer_forward, but the per-frame intermediates (8 * S * E bytes per frame) are kept in a fixed array inside
+ * the library's device image instead of an allocation, and the call itself performs no cudaMalloc / cudaFree.
+ *   - Limit: batch * 8 * S * E <= ITA_LAYER_STATIC_SCRATCH_BYTES (256 frames at S=128, E=64; 128 frames at E=128).  A larger
+ *     batch returns ITA_ERR_INVALID with the limit in ita_last_error(); it is never split or spilled.
+ *   - Cost: every GPU that loads libita_b200.so carries those 16 MiB until the process exits, used or not.
+ *   - The handle must run the single-head tcgen05 kernels for both blocks (ita_mha_fused_supported and
+ *     ita_ffn_fused_supported, H == 1); other handles get ITA_ERR_UNSUPPORTED because their kernels keep allocated scratch.
+ *     (ita_mha_create itself allocates the parameter copies: create handles at start-up.)
+ *   - The first call on each device resolves the array's device address; make it at start-up, before any stream capture.
+ *   - One array per GPU per process, shared by all handles and streams, never cleared (every intermediate is written in
+ *     full before it is read, so stale contents are harmless): calls that may overlap on the GPU race on it -- keep them
+ *     on one stream or order them with events. */
+#define ITA_LAYER_STATIC_SCRATCH_BYTES (16 * 1024 * 1024)
+ITA_API int ita_encoder_layer_forward_static(ita_mha_handle *h, const ita_layer_params *lp, const float *x_dev, float *y_dev,
+                                             int64_t batch, void *cuda_stream);
+
 /* The producer in front of the hot path: 60x90 depth frames -> 128 tokens of E channels (OverlapPatchMerging,
  * models/ITA/QAT/layers.py:25-45), all DEVICE pointers.  img_dev: [batch, 60, 90] uint8 (img_is_u8 != 0; scaled by 1/255 as
  * main.cpp:168 does) or float32.  conv_w_dev [E,1,7,7], conv_b_dev [E], ln_w_dev / ln_b_dev [E] as in the module's
