@@ -153,7 +153,9 @@ def params_from_captured_block(q, prefix: str = "b0_", round_mode: int = L.ROUND
     Follows the harness' recipe (``tests/export_and_validation_W_B.py:479-491,247-305``): ``W = weight.T[None]``,
     ``B = round(bias / (s_in * s_w))``, ``eff = s_in1 * s_in2 / s_out`` -> ``calculate_hw_params``; the fp32 requant scales
     are formed the way the backend forms them (``linear_eff_f32`` for Linear, double product cast to f32 for the matmuls).
-    H = 1 (every shipped model)."""
+    H = 1 for every shipped model; a capture that carries an ``H`` entry > 1 (``qat_block_H4_S256.npz``, the module
+    ``ITASelfAttention_QAT(128, 256, 4)``) is split the way the module splits it (``models/ITA/QAT/layers.py:110-123``): heads
+    are column slices of one projection, one out_proj over the concatenated contexts, every head shares the stage's scale."""
     g = lambda k: q[prefix + k]
     s = lambda k: float(q[prefix + k])
     P, E = g("q_proj_w").shape
@@ -180,6 +182,20 @@ def params_from_captured_block(q, prefix: str = "b0_", round_mode: int = L.ROUND
         # ReLU keeps the quantisation parameters (s_in == s_out): the golden model's relu requant is the identity
         mult[L.ST_RELU, 0] = 0
         kw = dict(F=F, Wff=T("fc1"), Wff2=T("fc2"), Bff=Bi("fc1"), Bff2=Bi("fc2"))
+    H = int(q["H"]) if "H" in q else 1
+    if H > 1:
+        if with_ffn or P % H:
+            raise ValueError("multi-head captures carry no FFN and need proj_dim divisible by num_heads")
+        hd = int(P) // H
+        split = lambda k: np.ascontiguousarray(np.asarray(g(k + "_w")).reshape(H, hd, E).transpose(0, 2, 1)).astype(np.int8)
+        Wo = np.ascontiguousarray(np.asarray(g("out_proj_w")).T.reshape(H, hd, E)).astype(np.int8)
+        Bo = np.zeros((H, int(E)), np.int32)
+        Bo[0] = Bi("out_proj")[0]
+        rep = lambda a: np.ascontiguousarray(np.repeat(a, H, axis=1))
+        return ITAQuantParams(S=S, E=int(E), P=hd, H=H, Wq=split("q_proj"), Wk=split("k_proj"), Wv=split("v_proj"), Wo=Wo,
+                              Bq=Bi("q_proj").reshape(H, hd), Bk=Bi("k_proj").reshape(H, hd), Bv=Bi("v_proj").reshape(H, hd), Bo=Bo,
+                              mult=rep(mult), shift=rep(shift), add=rep(add), eff=rep(eff), round_mode=round_mode,
+                              softmax_mode=softmax_mode, head_mode=L.HEADS_TORCH)
     return ITAQuantParams(S=S, E=int(E), P=int(P), H=1, Wq=T("q_proj"), Wk=T("k_proj"), Wv=T("v_proj"), Wo=T("out_proj"),
                           Bq=Bi("q_proj"), Bk=Bi("k_proj"), Bv=Bi("v_proj"), Bo=Bi("out_proj"), mult=mult, shift=shift, add=add,
                           eff=eff, round_mode=round_mode, softmax_mode=softmax_mode, head_mode=L.HEADS_PYITA, **kw)

@@ -177,6 +177,86 @@ def gen_qat_block(h, variant: str):
           {k: (v.shape if hasattr(v, 'shape') and getattr(v, 'ndim', 0) else v) for k, v in save.items() if k.startswith('b0_hw')})
 
 
+def gen_qat_block_h4(h):
+    """BASELINE config 3 as the reference module: ``ITASelfAttention_QAT(embed_dim=128, proj_dim=256, num_heads=4)``
+    (models/ITA/QAT/layers.py:79-127) on 256 tokens, standalone: prepare_qat -> calibrate -> convert (qnnpack), matmul2 patched as
+    tests/export_and_validation_W_B.py:408-423, every submodule output captured by forward hooks.  Pins the head split
+    (reshape(B,N,H,hd).permute, layers.py:110-113), the context merge and the single out_proj (layers.py:120-123).
+    Keys follow qat_block_*.npz (prefix b0_), stage outputs in the module's own layouts: q/k/v_proj_out [B,N,H*hd],
+    qk_out / softmax_out [B,H,N,N], av_out [B,H,N,hd], out_proj_out [B,N,E]."""
+    torch.manual_seed(4)
+    torch.backends.quantized.engine = "qnnpack"
+    from models.ITA.QAT.layers import ITASelfAttention_QAT, ita_symmetric_qconfig
+    E, PT, H, N, B = 128, 256, 4, 256, 2
+    m = ITASelfAttention_QAT(E, PT, H)
+    with torch.no_grad():
+        for lin in (m.q_proj, m.k_proj, m.v_proj, m.out_proj):
+            lin.weight.mul_(3.0)
+            lin.bias.normal_(0, 0.3)
+    m.qconfig = ita_symmetric_qconfig
+    mp = torch.ao.quantization.prepare_qat(m.train())
+    g = torch.Generator().manual_seed(9)
+    for _ in range(3):
+        mp(torch.randn(B, N, E, generator=g))
+    mc = torch.ao.quantization.convert(mp.eval())
+    mm2 = mc.matmul2
+    mc.matmul2.matmul = (lambda s, z: (lambda a, b: h.custom_quantized_matmul(a, b, output_scale=s, output_zero_point=z)))(mm2.scale,
+                                                                                                                         mm2.zero_point)
+    assert mc.num_heads == H and mc.head_dim == PT // H
+    cap = {}
+
+    def hook(name):
+        def f(mod, inp, out):
+            cap[name + "_in"] = inp[0].detach().clone()
+            cap[name + "_out"] = out.detach().clone()
+        return f
+
+    hs = [getattr(mc, n).register_forward_hook(hook(n)) for n in ("quant", "q_proj", "k_proj", "v_proj", "out_proj", "custom_softmax")]
+    x = torch.randn(B, N, E, generator=g)
+    with torch.no_grad():
+        y = mc(x)
+    for k in hs:
+        k.remove()
+    for n in ("quant", "q_proj", "k_proj", "v_proj", "out_proj", "custom_softmax"):
+        assert cap[n + "_out"].is_quantized and cap[n + "_out"].q_zero_point() == 0, n
+    pre = "b0_"
+    xq = cap["quant_out"]
+    save = {"H": H, "B": B, "x_float": x.numpy(), "y_float": y.numpy(), pre + "x": xq.int_repr().numpy(), pre + "s_x": xq.q_scale()}
+    for nm in ("q_proj", "k_proj", "v_proj", "out_proj"):
+        lin = getattr(mc, nm)
+        w = lin.weight()
+        assert w.qscheme() == torch.per_tensor_symmetric or w.q_zero_point() == 0
+        entry = {"bias": lin.bias().detach().numpy(), "input": [{"scale": cap[nm + "_in"].q_scale()}],
+                 "weight": {"scale": w.q_scale(), "q_value": w.int_repr().numpy()}}
+        save[pre + nm + "_w"] = w.int_repr().numpy().astype(np.int8)           # torch layout [out,in]
+        save[pre + nm + "_sw"] = w.q_scale()
+        save[pre + nm + "_bias"] = lin.bias().detach().numpy().astype(np.float32)
+        save[pre + nm + "_sin"] = cap[nm + "_in"].q_scale()
+        save[pre + nm + "_sout"] = float(lin.scale)
+        save[pre + nm + "_out"] = cap[nm + "_out"].int_repr().numpy().astype(np.int8)
+        save[pre + nm + "_bias_i32"] = h.dequantize_bias_to_int32(entry)
+        save[pre + "hw_" + nm] = np.array([*h.calculate_hw_params(cap[nm + "_in"].q_scale() * w.q_scale() / float(lin.scale)), 0], np.int64)
+    logits, probs, ctx = cap["custom_softmax_in"], cap["custom_softmax_out"], cap["out_proj_in"]
+    assert probs.dtype == torch.quint8 and logits.dtype == torch.qint8
+    save[pre + "qk_out"] = logits.int_repr().numpy().astype(np.int8)                         # [B,H,N,N]
+    save[pre + "qk_sout"] = logits.q_scale()
+    save[pre + "softmax_out"] = probs.int_repr().numpy().astype(np.uint8)
+    save[pre + "softmax_sout"] = probs.q_scale()
+    # context as out_proj sees it: [B,N,H*hd] (layers.py:121) -> per head [B,H,N,hd]
+    save[pre + "av_out"] = np.ascontiguousarray(ctx.int_repr().numpy().reshape(B, N, H, PT // H).transpose(0, 2, 1, 3)).astype(np.int8)
+    save[pre + "av_sout"] = ctx.q_scale()
+    save[pre + "hw_qk_matmul"] = np.array([*h.calculate_hw_params(float(mc.q_proj.scale) * float(mc.k_proj.scale) / logits.q_scale()), 0], np.int64)
+    save[pre + "hw_av_matmul"] = np.array([*h.calculate_hw_params(probs.q_scale() * float(mc.v_proj.scale) / ctx.q_scale()), 0], np.int64)
+    save["quant_scale"] = float(mc.quant.scale)
+    save["out_scale"] = float(mc.out_proj.scale)
+    assert abs(save[pre + "qk_sout"] - float(mc.matmul1.scale)) < 1e-12 and abs(save[pre + "av_sout"] - float(mc.matmul2.scale)) < 1e-12
+    np.savez_compressed(os.path.join(HERE, "qat_block_H4_S256.npz"), **save)
+    torch.save(mc.state_dict(), os.path.join(HERE, "qat_state_H4_S256.pt"))
+    sat = {k: float((np.abs(save[pre + k].astype(np.int32)) >= 127).mean()) for k in ("q_proj_out", "qk_out", "av_out", "out_proj_out")}
+    print("qat_block_H4_S256.npz: scales", {k: round(float(save[pre + k]), 5) for k in ("s_x", "q_proj_sout", "qk_sout", "av_sout", "out_proj_sout")},
+          "saturated share", sat, "softmax nonzero", float((save[pre + "softmax_out"] > 0).mean()))
+
+
 def gen_quantize():
     """QuantStub at the operator's float boundary (reference models/ITA/QAT/layers.py:103): torch.quantize_per_tensor over
     random floats and awkward scales (ties, saturation, denormal-ish scales)."""
@@ -300,6 +380,9 @@ def gen_model(h):
 if __name__ == "__main__":
     h = _import_harness()
     sys.path.insert(0, HERE)
+    if len(sys.argv) > 1 and sys.argv[1] == "--h4":      # the multi-head fixture added in round 3 (the others stay as committed)
+        gen_qat_block_h4(h)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "--new":     # only the fixtures added in round 2 (the others stay as committed)
         gen_quantize()
         gen_model(h)
@@ -308,3 +391,4 @@ if __name__ == "__main__":
     gen_hw_params(h)
     gen_qat_block(h, "E64")
     gen_qat_block(h, "E128")
+    gen_qat_block_h4(h)

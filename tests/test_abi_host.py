@@ -204,6 +204,25 @@ def test_module_state_dict_round_trip_and_reference_checkpoint(ita):
         m2.quant_params(128)
 
 
+def test_multi_head_reference_checkpoint_and_capture_agree(ita, R):
+    """The converted ``ITASelfAttention_QAT(128, 256, 4)`` of tests/golden/make_golden.py: its state_dict loaded into
+    ``ITASelfAttention``, its flattened capture through ``params_from_captured_block`` and the oracle-side recipe of
+    tests/test_oracle.py give the same multi-head parameter set (torch head convention, layers.py:110-123)."""
+    from test_oracle import _block_params_heads
+    q = np.load(os.path.join(GOLDEN, "qat_block_H4_S256.npz"))
+    want = ita.params_from_captured_block(q, "b0_")
+    assert (want.S, want.E, want.P, want.H, want.head_mode) == (256, 128, 64, 4, ita._lib.HEADS_TORCH)
+    o = _block_params_heads(R, q, "b0_", R.ROUND_TORCH_RNE_F32)
+    for k in ("Wq", "Wk", "Wv", "Wo", "Bq", "Bk", "Bv", "Bo", "eff"):
+        assert np.array_equal(getattr(want, k), getattr(o, k)), k
+    for st in (R.ST_Q, R.ST_K, R.ST_V, R.ST_QK, R.ST_AV, R.ST_O):
+        assert np.array_equal(want.mult[st], o.mult[st]) and np.array_equal(want.shift[st], o.shift[st]), st
+    m = ita.ITASelfAttention(128, 256, 4)
+    res = m.load_state_dict(torch.load(os.path.join(GOLDEN, "qat_state_H4_S256.pt"), weights_only=False), strict=False)
+    assert not res.unexpected_keys, res.unexpected_keys
+    _same_params(m.quant_params(256), want)
+
+
 def test_full_model_state_dict_reader_and_float_stages(ita):
     """``ITAViTLSTM.from_state_dict`` on a converted reference checkpoint: the int8 layer parameters equal the harness'
     recipe on the captured block, and the float pre/post stages (tokenizer; fusion, decoder, LSTM, head) reproduce the

@@ -65,6 +65,54 @@ def _block_params(R, q, pre, round_mode):
                        round_mode=round_mode)
 
 
+def _block_params_heads(R, q, pre, round_mode):
+    """Oracle parameter set of the captured MULTI-HEAD reference block (qat_block_H4_S256.npz): heads are column slices of
+    one projection and one out_proj runs over the concatenated contexts (layers.py:110-123) -> HEADS_TORCH; every head shares
+    the stage's scale."""
+    H = int(q["H"])
+    p1 = _block_params(R, q, pre, round_mode)                      # H = 1 view: [1,E,H*hd] weights, per-stage constants
+    PT, E = q[pre + "q_proj_w"].shape
+    hd = PT // H
+    split = lambda k: np.ascontiguousarray(q[pre + k + "_w"].reshape(H, hd, E).transpose(0, 2, 1))      # [H*hd,E] -> [H,E,hd]
+    bsplit = lambda k: q[pre + k + "_bias_i32"].astype(np.int32).reshape(H, hd)
+    Wo = np.ascontiguousarray(q[pre + "out_proj_w"].T.reshape(H, hd, E))                               # [E,H*hd] -> [H,hd,E]
+    Bo = np.zeros((H, E), np.int32)
+    Bo[0] = q[pre + "out_proj_bias_i32"]
+    rep = lambda a: np.ascontiguousarray(np.repeat(a, H, axis=1))
+    return R.ITAParams(S=p1.S, E=E, P=hd, H=H, Wq=split("q_proj"), Wk=split("k_proj"), Wv=split("v_proj"), Wo=Wo, Bq=bsplit("q_proj"),
+                       Bk=bsplit("k_proj"), Bv=bsplit("v_proj"), Bo=Bo, mult=rep(p1.mult), shift=rep(p1.shift), add=rep(p1.add),
+                       eff=rep(p1.eff), round_mode=round_mode, head_mode=R.HEADS_TORCH)
+
+
+def _heads_fixture_stage(q, pre, key, H):
+    """A stage of qat_block_H4_S256.npz in the oracle's layout: projections [B,N,H*hd] -> [B,H,N,hd]; the rest as stored."""
+    a = q[pre + key]
+    if key in ("q_proj_out", "k_proj_out", "v_proj_out"):
+        B, N, PT = a.shape
+        return np.ascontiguousarray(a.reshape(B, N, H, PT // H).transpose(0, 2, 1, 3))
+    return a
+
+
+def test_converted_multi_head_block_torch_rounding_bit_exact(R, RC):
+    """BASELINE config 3 as the reference module, ``ITASelfAttention_QAT(128, 256, 4)`` on 256 tokens, converted and captured by
+    tests/golden/make_golden.py: the oracle (torch head convention, torch rounding) reproduces EVERY stage bit-exactly, which
+    pins the head split / context merge / single out_proj of layers.py:110-123 to reference output."""
+    q = np.load(os.path.join(GOLDEN, "qat_block_H4_S256.npz"))
+    pre, H = "b0_", int(q["H"])
+    assert H == 4 and q[pre + "x"].shape == (2, 256, 128)
+    p = _block_params_heads(R, q, pre, R.ROUND_TORCH_RNE_F32)
+    assert (p.S, p.E, p.P, p.H) == (256, 128, 64, 4)
+    for impl in (lambda: R.mha_forward(p, q[pre + "x"]), lambda: RC.mha(p, q[pre + "x"])):
+        out = impl()
+        for k, fk in STAGE_FIX.items():
+            want = _heads_fixture_stage(q, pre, fk, H).reshape(out[k].shape)
+            assert np.array_equal(out[k], want), (k, int((out[k] != want).sum()))
+    # the float boundary: quant stub of the input, dequant of the output (layers.py:103,126)
+    xq = np.clip(np.rint(q["x_float"] / np.float32(q["quant_scale"])), -128, 127).astype(np.int8)
+    assert np.array_equal(xq, q[pre + "x"])
+    assert np.array_equal(q[pre + "out_proj_out"].astype(np.float32) * np.float32(q["out_scale"]), q["y_float"])
+
+
 STAGE_FIX = {"Qp": "q_proj_out", "Kp": "k_proj_out", "Vp": "v_proj_out", "A": "qk_out", "Asm": "softmax_out", "O": "av_out",
              "Y": "out_proj_out"}
 
