@@ -55,7 +55,12 @@ int mh_plan_create(ita_mha_handle *h, const ita_mha_desc *d) {
   const int E = h->E, P = h->P, H = h->H, S = h->S;
   if (S != kMhS) return no("multi-head tcgen05 kernel needs S == 256");
   if (!(P == 64 && E == 128)) return no("multi-head tcgen05 kernel is instantiated for E = 128, P = 64");
-  if (H < 1 || H > MhCfg<128, 64>::kMaxH) return no("multi-head tcgen05 kernel needs 1 <= H <= 8");
+  // k_ita_mh itself could walk up to MhCfg::kMaxH heads, but the output kernel is budgeted (three context tiles of H * P
+  // columns in shared memory; per head, H * E / 2 tensor-memory columns) and checked for at most MoCfg::kMaxH
+  static_assert(MoCfg<128, 64>::kMaxH <= MhCfg<128, 64>::kMaxH, "the output kernel's head limit is the pipeline's");
+  if (H < 1 || H > MoCfg<128, 64>::kMaxH)
+    return no("multi-head tcgen05 kernels run 1 <= H <= 4 heads (k_ita_mh_out keeps three context tiles of H * P columns in shared memory and, "
+              "in the per-head form, H * E / 2 tensor-memory columns per unit)");
   const bool per_head = (h->head_mode == ITA_HEADS_PYITA) && H > 1;
   if (per_head && H * E / 2 > 256) return no("per-head output projection needs H * E / 2 <= 256 tensor-memory columns per unit");
   int cc_major = 0, max_smem = 0;

@@ -199,18 +199,24 @@ class ITAViTLSTM(nn.Module):
     def _layer_engines(self, device: torch.device):
         key = device.index if device.index is not None else torch.cuda.current_device()
         if key not in self._engines:
-            engs = []
-            for i in range(self.num_layers):
-                if self.layer_params[i] is None:
-                    raise RuntimeError("ITAViTLSTM has no int8 parameters: load a converted state dict first")
-                eng = ITAEngine(self.layer_params[i], torch.device("cuda", key))
-                sc = self.layer_scales[i]
-                lp = eng.layer_params(sc["s_attn_in"], sc["s_attn_out"], sc["s_ffn_in"], sc["s_ffn_out"], self.norms1[i].weight.detach(),
-                                      self.norms1[i].bias.detach(), self.norms2[i].weight.detach(), self.norms2[i].bias.detach(),
-                                      self.norms1[i].eps)
-                engs.append((eng, lp))
-            self._engines[key] = engs
+            self._engines[key] = self._build_engines(key)
         return self._engines[key]
+
+    def _build_engines(self, key: int) -> list:
+        """A fresh set of per-layer handles on device ``key`` (each owns its device scratch).  ``_layer_engines`` caches one set
+        per device for eager calls; ``GraphedStep`` takes a private set, because a captured graph holds the raw addresses of the
+        handles' scratch buffers and an eager call at a larger batch reallocates those of the shared set."""
+        engs = []
+        for i in range(self.num_layers):
+            if self.layer_params[i] is None:
+                raise RuntimeError("ITAViTLSTM has no int8 parameters: load a converted state dict first")
+            eng = ITAEngine(self.layer_params[i], torch.device("cuda", key))
+            sc = self.layer_scales[i]
+            lp = eng.layer_params(sc["s_attn_in"], sc["s_attn_out"], sc["s_ffn_in"], sc["s_ffn_out"], self.norms1[i].weight.detach(),
+                                  self.norms1[i].bias.detach(), self.norms2[i].weight.detach(), self.norms2[i].bias.detach(),
+                                  self.norms1[i].eps)
+            engs.append((eng, lp))
+        return engs
 
     @torch.no_grad()
     def tokens(self, img: torch.Tensor, want_q: bool = False):
@@ -246,9 +252,10 @@ class ITAViTLSTM(nn.Module):
         return self.tokenizer_norm(x.flatten(2).transpose(1, 2)).contiguous()
 
     @torch.no_grad()
-    def encode(self, x: torch.Tensor) -> torch.Tensor:
-        """The encoder stack on f32 tokens [B,128,E] (``QAT/model.py:100-113``): libita_b200 only."""
-        for eng, lp in self._layer_engines(x.device):
+    def encode(self, x: torch.Tensor, engines: Optional[list] = None) -> torch.Tensor:
+        """The encoder stack on f32 tokens [B,128,E] (``QAT/model.py:100-113``): libita_b200 only.  ``engines``: a private set
+        from ``_build_engines`` instead of the model's cached one (``GraphedStep``)."""
+        for eng, lp in (engines if engines is not None else self._layer_engines(x.device)):
             x = eng.layer(x, lp)
         return x
 
@@ -298,13 +305,13 @@ class ITAViTLSTM(nn.Module):
         return self.nn_fc2(xs), (hn, cn)
 
     @torch.no_grad()
-    def forward(self, X: list):
+    def forward(self, X: list, _engines: Optional[list] = None):
         X = refine_inputs(list(X))
         img, vel, quat = X[0], X[1], X[2]
         if not img.is_cuda:
             raise ValueError("ITAViTLSTM runs on CUDA tensors only (no CPU fallback)")
         hidden = X[3] if len(X) > 3 else None
-        return self.head(self.encode(self.tokens(img)), vel.float(), quat.float(), hidden)
+        return self.head(self.encode(self.tokens(img), _engines), vel.float(), quat.float(), hidden)
 
 
 class GraphedStep:
@@ -312,7 +319,9 @@ class GraphedStep:
     fusion conv, decoder / LSTM GEMMs, cell kernels) become one graph launch, which is what bounds the latency of the small
     batches a serving loop sees (batch 1: ~270 us eager).  Inputs are copied into static device buffers, the LSTM state lives in
     the step's own buffers between calls (``reset_state`` zeroes it), outputs are views of static buffers (copy before the next
-    call if they must survive it).
+    call if they must survive it).  The graph holds raw device addresses of the encoder handles' scratch buffers, so the step
+    owns a PRIVATE set of handles, used at this one batch size only: eager calls on the same model (``DroneServer.infer`` at any
+    batch) can grow and reallocate the model's shared handles without touching what the graph replays.  ``close()`` frees them.
 
         step = GraphedStep(model, batch=8, device=torch.device("cuda", 0))
         cmd = step(img_u8, vel, quat)            # [8, 3]; state carried inside
@@ -328,16 +337,17 @@ class GraphedStep:
         self.quat = torch.zeros((batch, 4), dtype=torch.float32, device=device)
         self.h = torch.zeros((L_, batch, Hd), dtype=torch.float32, device=device)
         self.c = torch.zeros_like(self.h)
+        self._engines = model._build_engines(device.index if device.index is not None else torch.cuda.current_device())
         side = torch.cuda.Stream(device)
         side.wait_stream(torch.cuda.current_stream(device))
         with torch.cuda.stream(side):                     # warm-up off the capture: handles, scratch buffers, cuBLAS workspaces
             for _ in range(3):
-                model([self.img, self.vel, self.quat, (self.h, self.c)])
+                model([self.img, self.vel, self.quat, (self.h, self.c)], _engines=self._engines)
         torch.cuda.current_stream(device).wait_stream(side)
         torch.cuda.synchronize(device)
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            out, (hn, cn) = model([self.img, self.vel, self.quat, (self.h, self.c)])
+            out, (hn, cn) = model([self.img, self.vel, self.quat, (self.h, self.c)], _engines=self._engines)
             self.h.copy_(hn)
             self.c.copy_(cn)
             self.out = out
@@ -346,6 +356,13 @@ class GraphedStep:
     def reset_state(self) -> None:
         self.h.zero_()
         self.c.zero_()
+
+    def close(self) -> None:
+        """Drop the graph, then free the private handles it replays on."""
+        self.graph = None
+        for eng, _ in self._engines:
+            eng.close()
+        self._engines = []
 
     @torch.no_grad()
     def __call__(self, img: torch.Tensor, vel: torch.Tensor, quat: torch.Tensor) -> torch.Tensor:

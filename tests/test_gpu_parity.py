@@ -237,6 +237,30 @@ def test_reference_fixture_bit_exact_on_gpu(ita, R, variant, blocks):
         eng.close()
 
 
+def test_reference_multi_head_fixture_bit_exact_on_gpu(ita, R):
+    """BASELINE config 3 pinned to the reference: the converted ``ITASelfAttention_QAT(128, 256, 4)`` on 256 tokens captured in
+    tests/golden/qat_block_H4_S256.npz (generated by importing the reference).  The multi-head tcgen05 kernels (k_ita_mh +
+    k_ita_mh_out, torch head convention) and the staged kernels reproduce EVERY stage of the reference bit-exactly, and the
+    module built from the reference's converted state_dict returns the reference's float output."""
+    from test_oracle import STAGE_FIX, _heads_fixture_stage
+    q = np.load(os.path.join(GOLDEN, "qat_block_H4_S256.npz"))
+    pre, H = "b0_", int(q["H"])
+    eng = ita.ITAEngine(ita.params_from_captured_block(q, pre), _dev())
+    assert eng.fused_supported and "k_ita_mh" in eng.describe(), eng.describe()
+    x = torch.from_numpy(q[pre + "x"]).to(_dev())
+    for fused in (True, False):
+        st = eng.forward_stages(x, fused_debug=fused)
+        for k, fk in STAGE_FIX.items():
+            _cmp(st[k], _heads_fixture_stage(q, pre, fk, H), f"H=4 fixture {'tcgen05' if fused else 'staged'} {k}")
+    _cmp(eng.forward(x), q[pre + "out_proj_out"], "H=4 fixture forward")
+    eng.sync_check()
+    eng.close()
+    m = ita.ITASelfAttention(128, 256, 4)
+    m.load_state_dict(torch.load(os.path.join(GOLDEN, "qat_state_H4_S256.pt"), weights_only=False), strict=False)
+    y = m(torch.from_numpy(q["x_float"]).to(_dev()))
+    assert np.array_equal(y.cpu().numpy(), q["y_float"])
+
+
 def test_itamax_fixture_on_gpu(ita, R):
     """Reference IntegerApproximatedSoftmaxFn vectors through the CUDA ITAmax step (ita_mha_step STEP4_SOFTMAX)."""
     g = np.load(os.path.join(GOLDEN, "itamax_repo.npz"))
@@ -688,6 +712,21 @@ def test_graphed_model_step_equals_eager(ita, R):
     assert torch.equal(step.h, hidden[0]) and torch.equal(step.c, hidden[1])
     step.reset_state()
     assert float(step.h.abs().max()) == 0.0
+    # An eager call at a LARGER batch on the same model grows (frees and reallocates) the scratch of the model's shared handles.
+    # The graph replays on the step's private handles, so it must neither fault nor change its answer.
+    big = 8 * B + 3
+    m([torch.randint(0, 256, (big, 60, 90), generator=g, dtype=torch.uint8).to(_dev()), torch.rand((big, 1), generator=g).to(_dev()),
+       torch.rand((big, 4), generator=g).to(_dev())])
+    junk = torch.full((64 << 20,), 0x55, dtype=torch.uint8, device=_dev())       # recycle whatever the reallocation released
+    img = torch.randint(0, 256, (B, 60, 90), generator=g, dtype=torch.uint8).to(_dev())
+    vel, quat = (torch.rand((B, 1), generator=g) * 5).to(_dev()), torch.rand((B, 4), generator=g).to(_dev())
+    want, _ = m([img, vel, quat])
+    got = step(img, vel, quat)
+    torch.cuda.synchronize()
+    assert torch.equal(got, want), (got - want).abs().max().item()
+    assert all(e is not s_ for (e, _), (s_, _) in zip(m._layer_engines(_dev()), step._engines))
+    del junk
+    step.close()
 
 
 # ----------------------------------------------------------------------------------------------------- full-size properties
@@ -772,6 +811,12 @@ def test_multi_head_limits_and_fallbacks(ita, R, RC):
     assert not eng.fused_supported and "shared memory" in eng.fused_unsupported_reason(), eng.fused_unsupported_reason()
     y = eng.forward(torch.from_numpy(X).to(_dev()))                     # PATH_AUTO -> staged (says so once on stderr)
     _cmp(y, RC.mha(p8, X, intermediates=False)["Y"], "8 heads, concatenated (staged)")
+    eng.close()
+    # 5 and 6 heads would fit the shared memory of the concatenated form, but the pipelines are budgeted and checked up to 4
+    p5 = R.make_synthetic(256, 128, 64, 5, seed=22, head_mode=1)
+    eng = _engine(ita, p5)
+    assert not eng.fused_supported and "H <= 4" in eng.fused_unsupported_reason(), eng.fused_unsupported_reason()
+    _cmp(eng.forward(torch.from_numpy(X).to(_dev())), RC.mha(p5, X, intermediates=False)["Y"], "5 heads, concatenated (staged)")
     eng.close()
     p8p = R.make_synthetic(256, 128, 64, 8, seed=21, head_mode=0)
     eng = _engine(ita, p8p)
