@@ -93,6 +93,70 @@ def final_velocity(raw: np.ndarray, desired_vel: np.ndarray, pos_x: np.ndarray) 
     return v
 
 
+# ------------------------------------------------------------------------------------------------------ per-client state
+class ClientStates:
+    """LSTM state of every known client in ONE pair of device tensors ``[L, slots, Hd]`` plus an ``addr -> slot`` table, so
+    that a batch gathers its states with one ``index_select`` and stores them with one ``index_copy_`` (separate small tensors
+    per client cost two ``torch.stack`` over the batch and two clones per client: thousands of tiny launches at a 4096-frame
+    batch, several times the model step).  Reads like a mapping ``addr -> (h [L,Hd], c [L,Hd], last_seen)``."""
+
+    def __init__(self, layers: int, hidden: int, device: torch.device, capacity: int = 64):
+        self.L, self.Hd, self.device = int(layers), int(hidden), torch.device(device)
+        self.h = torch.zeros((self.L, capacity, self.Hd), device=self.device)
+        self.c = torch.zeros_like(self.h)
+        self.slot: Dict[Tuple, int] = {}
+        self.seen: Dict[Tuple, float] = {}
+        self.free: List[int] = list(range(capacity - 1, -1, -1))
+
+    def __len__(self) -> int:
+        return len(self.slot)
+
+    def __contains__(self, addr) -> bool:
+        return addr in self.slot
+
+    def __getitem__(self, addr):
+        i = self.slot[addr]
+        return self.h[:, i], self.c[:, i], self.seen[addr]
+
+    def _grow(self, need: int) -> None:
+        cap = self.h.shape[1]
+        new = max(2 * cap, cap + need)
+        for name in ("h", "c"):
+            t = torch.zeros((self.L, new, self.Hd), device=self.device)
+            t[:, :cap] = getattr(self, name)
+            setattr(self, name, t)
+        self.free = list(range(new - 1, cap - 1, -1)) + self.free
+
+    def slots_for(self, addrs: Sequence[Tuple], now: float) -> torch.Tensor:
+        """Slot index of every address (device int64 [n]); unknown clients get a zeroed slot."""
+        fresh = [a for a in addrs if a not in self.slot]
+        if len(fresh) > len(self.free):
+            self._grow(len(fresh) - len(self.free))
+        new_slots = []
+        for a in fresh:
+            self.slot[a] = self.free.pop()
+            new_slots.append(self.slot[a])
+        if new_slots:                                   # a recycled slot still holds its previous owner's state
+            z = torch.tensor(new_slots, device=self.device)
+            self.h.index_fill_(1, z, 0.0)
+            self.c.index_fill_(1, z, 0.0)
+        for a in addrs:
+            self.seen[a] = now
+        return torch.tensor([self.slot[a] for a in addrs], dtype=torch.int64, device=self.device)
+
+    def gather(self, idx: torch.Tensor):
+        return self.h.index_select(1, idx), self.c.index_select(1, idx)
+
+    def scatter(self, idx: torch.Tensor, h: torch.Tensor, c: torch.Tensor) -> None:
+        self.h.index_copy_(1, idx, h.to(self.h.dtype))
+        self.c.index_copy_(1, idx, c.to(self.c.dtype))
+
+    def expire(self, now: float, ttl_s: float) -> None:
+        for a in [a for a, t in self.seen.items() if now - t > ttl_s]:
+            self.free.append(self.slot.pop(a))
+            del self.seen[a]
+
+
 # ------------------------------------------------------------------------------------------------------------ the server
 class DroneServer:
     """Batched UDP inference service.
@@ -107,7 +171,7 @@ class DroneServer:
         self.model, self.device = model, torch.device(device)
         self.max_batch, self.prescale_velocity, self.quat_stride = int(max_batch), bool(prescale_velocity), int(quat_stride)
         self.L, self.Hd, self.state_ttl_s = int(lstm_layers), int(lstm_hidden), float(state_ttl_s)
-        self.state: Dict[Tuple, Tuple[torch.Tensor, torch.Tensor, float]] = {}     # addr -> (h [L,Hd], c [L,Hd], last seen)
+        self.state = ClientStates(self.L, self.Hd, self.device)                    # addr -> (h [L,Hd], c [L,Hd], last seen)
         self.sock = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
         self.sock.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
         try:
@@ -136,18 +200,11 @@ class DroneServer:
         v_in = vel / np.float32(10.0) if self.prescale_velocity else vel
         v_t = torch.from_numpy(np.ascontiguousarray(v_in.reshape(n, 1))).to(dev, non_blocking=True)
         q_t = torch.from_numpy(np.ascontiguousarray(quat)).to(dev, non_blocking=True)
-        h = torch.zeros((self.L, n, self.Hd), device=dev)
-        c = torch.zeros((self.L, n, self.Hd), device=dev)
-        known = [i for i, a in enumerate(addrs) if a in self.state]
-        if known:
-            idx = torch.tensor(known, device=dev)
-            h[:, idx] = torch.stack([self.state[addrs[i]][0] for i in known], dim=1)
-            c[:, idx] = torch.stack([self.state[addrs[i]][1] for i in known], dim=1)
+        idx = self.state.slots_for(addrs, time.monotonic())        # new clients start from a zero state
+        h, c = self.state.gather(idx)                              # one index_select each, whatever the batch
         with torch.no_grad():
             cmd, (hn, cn) = self.model([img, v_t, q_t, (h, c)])
-        now = time.monotonic()
-        for i, a in enumerate(addrs):
-            self.state[a] = (hn[:, i].clone(), cn[:, i].clone(), now)
+        self.state.scatter(idx, hn, cn)                            # one index_copy_ each
         out = final_velocity(cmd.float().cpu().numpy(), vel, posx)
         self.frames += n
         self.batches += 1
@@ -192,9 +249,7 @@ class DroneServer:
         return served
 
     def expire(self) -> None:
-        now = time.monotonic()
-        for a in [a for a, (_, _, t) in self.state.items() if now - t > self.state_ttl_s]:
-            del self.state[a]
+        self.state.expire(time.monotonic(), self.state_ttl_s)
 
     def serve(self, max_frames: Optional[int] = None, idle_timeout_s: Optional[float] = None) -> int:
         """The loop (``while (true)`` at main.cpp:150); ends after ``max_frames`` frames or ``idle_timeout_s`` without traffic
@@ -226,7 +281,11 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
     args = ap.parse_args(argv)
     from .model import ITAViTLSTM
     dev = torch.device("cuda", args.device)
-    sd = dict(torch.load(args.checkpoint, weights_only=False))
+    try:                                      # plain tensors / packed-parameter tuples load without running pickled code
+        sd = dict(torch.load(args.checkpoint, weights_only=True))
+    except Exception as e:
+        raise SystemExit(f"{args.checkpoint}: not loadable with weights_only=True ({type(e).__name__}: {e}); re-save the converted "
+                         "model's state_dict() from a trusted environment, this loader does not unpickle arbitrary objects")
     model = ITAViTLSTM.from_state_dict(sd).to(dev)
     srv = DroneServer(model, dev, args.host, args.port, args.max_batch, quat_stride=args.quat_stride)
     print(f"serving on {srv.address[0]}:{srv.address[1]} (device {dev})", flush=True)

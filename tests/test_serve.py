@@ -120,9 +120,16 @@ def test_server_batches_clients_and_keeps_per_client_state():
     # short datagrams are dropped, the loop keeps running
     clients[0].sendto(b"junk", ("127.0.0.1", port))
     assert srv.poll(0.2) == 0
-    srv.state[("10.0.0.1", 1)] = (torch.zeros(3, 128), torch.zeros(3, 128), -1e9)
+    srv.state.slots_for([("10.0.0.1", 1)], now=-1e9)       # a client last seen long ago
+    assert ("10.0.0.1", 1) in srv.state and len(srv.state) == 4
     srv.expire()
-    assert ("10.0.0.1", 1) not in srv.state
+    assert ("10.0.0.1", 1) not in srv.state and len(srv.state) == 3
+    # the freed slot is recycled with a zero state, and the table grows past its first capacity
+    many = [("10.0.1.%d" % i, 7) for i in range(200)]
+    idx = srv.state.slots_for(many, now=0.0)
+    assert len(set(idx.tolist())) == 200 and len(srv.state) == 203
+    h0, c0 = srv.state.gather(idx)
+    assert float(h0.abs().max()) == 0.0 and float(c0.abs().max()) == 0.0
     for c in clients:
         c.close()
     srv.close()
